@@ -1,0 +1,143 @@
+/*
+ * b200nst.h -- C ABI of libb200nst.so: the B200 (sm_100a) per-frame stylisation hot path.
+ *
+ * The reference (TrentMahaffey/NeuralStyleTransferV1) has no FFI of its own: the seam is the
+ * Python nn.Module protocol.  Each entry point below names the reference interface it stands
+ * behind.  All pointers are raw; device pointers are marked [dev], host pointers [host].
+ * Every function returns 0 on success or a negative nst_status; the message is available from
+ * nst_last_error() (thread local).  No function synchronises the device or the stream unless
+ * stated; all work is enqueued on the caller's cudaStream_t (passed as void*).
+ *
+ * A handle is bound to one device and one model; it is not re-entrant.  Distinct handles are
+ * independent (one per GPU / worker).
+ */
+#ifndef B200NST_H_
+#define B200NST_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct nst_handle nst_handle;
+
+enum nst_status {
+  NST_OK = 0,
+  NST_ERR_INVALID = -1,      /* bad argument / unsupported shape */
+  NST_ERR_CUDA = -2,         /* CUDA runtime error (message has the cudaError string) */
+  NST_ERR_WEIGHTS = -3,      /* missing / mis-shaped tensor in nst_load_weights */
+  NST_ERR_STATE = -4,        /* call order violated (e.g. forward before weights) */
+  NST_ERR_WORKSPACE = -5     /* workspace too small */
+};
+
+/* architectures */
+enum nst_arch {
+  NST_ARCH_JOHNSON = 0,      /* transformer_net.TransformerNet        (transformer_net.py:4-41)     */
+  NST_ARCH_NST = 1,          /* transformer_net_nst.TransformerNet    (transformer_net_nst.py:62-127) */
+  NST_ARCH_RECONET = 2       /* model.ReCoNet(frn=False)              (model.py:107-116)            */
+};
+
+/* conv operand precision (fp32 accumulate and fp32 activation storage in every mode) */
+enum nst_precision {
+  NST_PREC_F16 = 0,          /* fp16 MMA operands, 1 tcgen05.mma term  (default; meets max|d|<=2, PSNR>=45) */
+  NST_PREC_F16X3 = 1,        /* fp16 hi+lo split operands, 3 terms (fp32-class accuracy)              */
+  NST_PREC_BF16 = 2,         /* bf16 operands, 1 term (north_star wording; misses the tolerance)      */
+  NST_PREC_FP32_DIRECT = 3   /* no tensor cores: fp32 FFMA direct-conv kernels (debug / validation)   */
+};
+
+/* composite mode of the mask alpha-composite (pipeline.py:2040-2043) */
+enum nst_composite_mode { NST_COMPOSITE_KEEP = 0, NST_COMPOSITE_REPLACE = 1 };
+
+/* ---- lifetime ------------------------------------------------------------------------------ */
+
+/* Replaces: `TransformerNet().to(device)` / `ReCoNet().to(device)` (pipeline.py:602,617).
+ * Fails with NST_ERR_CUDA when `device` is not an sm_100 GPU: there is no CPU fallback. */
+int nst_create(int device, int arch, int precision, nst_handle** out);
+void nst_destroy(nst_handle* h);
+
+/* Replaces: `model.load_state_dict(state)` (pipeline.py:568, :91).
+ * names[i] are the reference state_dict keys; ptrs[i] are [host] fp32, contiguous,
+ * in the reference layout (Conv2d OIHW, ConvTranspose2d IOHW, norm weight/bias [C]);
+ * shapes is 4 int64 per tensor (unused trailing dims = 1).  Unknown keys are ignored and counted
+ * in *n_unexpected; absent keys are counted in *n_missing (both may be NULL).  Weights are
+ * repacked once into library-owned device memory (fp16 hi/lo K-major tiles + fp32 copies).
+ * Synchronises the device. */
+int nst_load_weights(nst_handle* h, int n_tensors, const char* const* names,
+                     const float* const* ptrs, const int64_t* shapes,
+                     int* n_missing, int* n_unexpected);
+
+/* Output spatial size for an input of H x W: Johnson/ReCoNet 4*ceil(ceil(H/2)/2), NST H. */
+int nst_output_shape(const nst_handle* h, int H, int W, int* Ho, int* Wo);
+
+/* Bytes of [dev] workspace a forward with batch N, H x W needs (activations + statistics). */
+int nst_workspace_bytes(nst_handle* h, int N, int H, int W, size_t* bytes);
+
+/* ---- forward ------------------------------------------------------------------------------- */
+
+/* Replaces: `y = model(x_in)` (pipeline.py:1474; transformer_net.py:29-41).
+ * x: [dev] fp32 NCHW [N,3,H,W], already io-preset-normalised; y: [dev] fp32 NCHW [N,3,Ho,Wo].
+ * workspace: [dev], >= nst_workspace_bytes, 256-byte aligned. */
+int nst_forward_f32_nchw(nst_handle* h, const float* x, float* y, int N, int H, int W,
+                         void* workspace, size_t workspace_bytes, void* stream);
+
+/* Fused uint8 path; replaces ToTensor -> io_preset pre -> model -> io_preset post -> clamp ->
+ * [mask composite | uniform blend] -> ToPILImage pack (pipeline.py:1086-1099,1447-1486,
+ * 2040-2043,2089-2094; lib.py:27-51).
+ *   net_in[c]  = in_scale[c] * u8[src_c] + in_shift[c]     (src_c = 2-c when swap_rb)
+ *   out01[c]   = clamp(out_scale[c] * net_out[c'] + out_shift[c], 0, 1)   (c' = 2-c when swap_rb)
+ *   if mask:   a = mask[n,h,w]; out01 = clamp(keep ? a*out01+(1-a)*orig : (1-a)*out01+a*orig)
+ *   elif 0 <= blend < 1: out01 = clamp(blend*out01 + (1-blend)*orig)       (orig = u8/255)
+ *   y_u8 = trunc(out01 * 255)
+ * x,y: [dev] uint8 NHWC [N,H,W,3]; requires H,W multiples of 4 (Johnson/ReCoNet) so Ho==H.
+ * mask: [dev] fp32 [N,H,W] or NULL. */
+int nst_forward_u8_nhwc(nst_handle* h, const uint8_t* x, uint8_t* y, int N, int H, int W,
+                        const float in_scale[3], const float in_shift[3],
+                        const float out_scale[3], const float out_shift[3], int swap_rb,
+                        float blend, const float* mask, int composite_mode,
+                        void* workspace, size_t workspace_bytes, void* stream);
+
+/* ---- compositing --------------------------------------------------------------------------- */
+
+/* Replaces: region_blend.composite_regions / composite_regions_advanced
+ * (region_blend.py:1049-1108, 1589-1679), single scale:
+ *   out = clamp( sum_r m_r * (sum_j w[r][j] * S[idx[r][j]]) / max(sum_r m_r, 1e-6), 0, 1)
+ * srcs: K [dev] pointers to uint8 NHWC [H,W,3] frames (value/255); index -1 selects `original`.
+ * masks: [dev] fp32 [R,H,W].  region_idx / region_w: [host] R*J entries (J = terms per region).
+ * out: [dev] uint8 NHWC (truncating pack).  R <= 16, J <= 4, K <= 8. */
+int nst_composite_regions_u8(const uint8_t* const* srcs, int K, const uint8_t* original,
+                             const float* masks, int R, int J,
+                             const int* region_idx, const float* region_w,
+                             uint8_t* out, int H, int W, void* stream);
+
+/* Same, fp32 CHW planes in 0..1 in and out (the reference's tensor form). */
+int nst_composite_regions_f32(const float* const* srcs, int K, const float* original,
+                              const float* masks, int R, int J,
+                              const int* region_idx, const float* region_w,
+                              float* out, int H, int W, void* stream);
+
+/* ---- introspection ------------------------------------------------------------------------- */
+
+/* Number of conv layers of the model, and per-layer facts of the last plan (after a forward or
+ * nst_workspace_bytes): algorithmic FLOPs (2*Ho*Wo*Cout*Cin*k*k*N), algorithmic bytes, and which
+ * kernel runs it (0 = direct fp32, 1 = tcgen05).  Arrays are caller-allocated, length >= n. */
+int nst_num_layers(const nst_handle* h);
+int nst_layer_info(const nst_handle* h, int layer, char* name, int name_cap,
+                   double* flops, double* bytes, int* kernel_kind);
+
+/* Time each layer of one forward with CUDA events on `stream` (synchronises).  ms has
+ * nst_num_layers entries. */
+int nst_profile_layers_u8(nst_handle* h, const uint8_t* x, uint8_t* y, int N, int H, int W,
+                          void* workspace, size_t workspace_bytes, void* stream, float* ms);
+
+/* Number of kernels this library has launched on behalf of `h` since creation. */
+long long nst_launch_count(const nst_handle* h);
+
+const char* nst_last_error(void);
+const char* nst_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200NST_H_ */

@@ -1,0 +1,14 @@
+"""B200-native (sm_100a) per-frame stylisation hot path of TrentMahaffey/NeuralStyleTransferV1.
+
+Public surface (mirrors the reference's):
+  TransformerNet, TransformerNetNST, ReCoNet, ReCoNetModel   -- drop-in nn.Modules
+  Engine, composite_regions, io_preset_affine                -- the fast uint8 / compositing API
+  sharding.shard_range                                        -- frame-batch partitioning over GPUs
+"""
+from .engine import Engine, composite_regions, io_preset_affine  # noqa: F401
+from .modules import ReCoNet, TransformerNet, TransformerNetNST  # noqa: F401
+from .reconet_model import ReCoNetModel  # noqa: F401
+from .sharding import shard_range, shard_sizes  # noqa: F401
+
+__all__ = ["Engine", "composite_regions", "io_preset_affine", "TransformerNet", "TransformerNetNST",
+           "ReCoNet", "ReCoNetModel", "shard_range", "shard_sizes"]

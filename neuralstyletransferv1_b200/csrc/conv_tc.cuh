@@ -1,0 +1,56 @@
+// Host/device shared description of the tcgen05 implicit-GEMM conv tiling (see conv_tc.cu).
+#pragma once
+#include "nst_kernels.cuh"
+
+namespace nst {
+
+constexpr int TC_MAX_ENT = 81;          // tap entries per channel chunk (9x9 conv)
+constexpr int TC_PROD_WARPS = 8;
+constexpr int TC_PROD_THREADS = TC_PROD_WARPS * 32;
+constexpr int TC_FIRST_EPI_WARP = 2;
+constexpr int TC_FIRST_PROD_WARP = 6;
+constexpr int TC_THREADS = (TC_FIRST_PROD_WARP + TC_PROD_WARPS) * 32;   // 448
+constexpr int TC_MAX_A_STAGES = 4;
+constexpr int TC_MAX_B_STAGES = 8;
+constexpr int TC_SMEM_LIMIT = 227 * 1024;
+
+// GEMM view of one layer:  D[m, co] = sum_{entry e, k} A[m + ent_off[e], k] * W[e][k][co]
+//   m      : flat position inside the CTA tile's halo buffer (pitch P), M = MB*128 rows
+//   entry  : one filter tap (or a horizontal PAIR of taps for the 3-channel first layer)
+// A lives in shared memory as [term][plane = 8-channel group][position][8 x f16] (UMMA no-swizzle
+// K-major core matrices: 8 rows x 16 bytes, SBO = 128 B, LBO = plane stride), so a tap shift is a
+// plain byte offset on the descriptor start address.
+struct TcPlan {
+  int TH, TW, P, MB;
+  int NPOS;                 // positions per plane
+  int SUBPOS;               // stride-2 layers: positions per parity sub-plane
+  int halo_h, halo_w;       // input halo extent in conv-padded space
+  int tiles_x, tiles_y, num_tiles;     // num_tiles includes the batch
+  int CK, nchunks, planes;  // channels per chunk, chunks, 8-channel planes per chunk
+  int nent;                 // tap entries per chunk
+  int k16_per_ent;          // MMA K-steps per entry
+  int pair_mode;            // first layer: K = 2 adjacent pixels x 8 (3 real) channels
+  int NPAD;                 // UMMA N (Cout padded to a multiple of 16)
+  int tg, ngroups;          // entries per weight stage, stages per chunk
+  int a_stages, b_stages;
+  int nterms;               // 1, or 3 (hi*hi + lo*hi + hi*lo)
+  int a_tplanes, b_tplanes; // operand planes kept (1, or 2 = hi and lo)
+  int is_bf16;
+  int dbg;                  // debug bits: 1 = swap LBO/SBO roles in the UMMA descriptors
+  uint32_t a_plane_bytes, a_term_bytes, a_stage_bytes;
+  uint32_t b_ent_bytes, b_term_bytes, b_stage_bytes;
+  uint32_t smem_bytes;
+  int ent_off[TC_MAX_ENT];  // A position offset of each entry
+};
+
+struct TcArgs {
+  ConvParams p;
+  TcPlan t;
+  const void* wpack;        // [chunk][group][term][entry in group][plane][NPAD][8] 16-bit
+  unsigned int* err_flag;   // set non-zero when a pipeline wait times out
+};
+
+cudaError_t launch_conv_tc(const TcArgs& a, int num_sms, cudaStream_t stream);
+cudaError_t conv_tc_init();
+
+}  // namespace nst

@@ -1,0 +1,808 @@
+// C ABI of libb200nst.so (include/b200nst.h): handle, weight repacking, per-shape planning and
+// the layer-by-layer forward of the three generator families.
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <cmath>
+#include <map>
+#include <string>
+#include <vector>
+#include <algorithm>
+
+#include "../../include/b200nst.h"
+#include "conv_tc.cuh"
+
+namespace nst {
+cudaError_t launch_conv_direct(const ConvParams& p, const float* wdir, cudaStream_t stream);
+
+constexpr int COMP_MAX_R = 16;
+constexpr int COMP_MAX_J = 4;
+constexpr int COMP_MAX_K = 8;
+struct CompositeArgs {
+  const void* srcs[COMP_MAX_K];
+  const void* original;
+  const float* masks;
+  void* out;
+  int K, R, J, H, W;
+  int idx[COMP_MAX_R * COMP_MAX_J];
+  float w[COMP_MAX_R * COMP_MAX_J];
+};
+cudaError_t launch_composite(const CompositeArgs& a, bool u8, cudaStream_t stream);
+}  // namespace nst
+
+using namespace nst;
+
+// ---------------------------------------------------------------------------------------------
+// errors
+// ---------------------------------------------------------------------------------------------
+static thread_local char g_err[512] = "";
+
+static int fail(int code, const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+  return code;
+}
+#define CUDA_TRY(expr)                                                                         \
+  do {                                                                                         \
+    cudaError_t _e = (expr);                                                                   \
+    if (_e != cudaSuccess) return fail(NST_ERR_CUDA, "%s: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, __LINE__); \
+  } while (0)
+
+// ---------------------------------------------------------------------------------------------
+// model description
+// ---------------------------------------------------------------------------------------------
+enum { BUF_IMAGE = -1, B_R1 = 0, B_R2, B_T1, B_T2, B_YA, B_YB, NBUF };
+
+struct LayerSpec {
+  std::string name;
+  std::string wkey, bkey;        // conv weight / bias
+  std::string in_gkey, in_bkey;  // InstanceNorm affine applied to the SOURCE tensor (previous layer's norm)
+  int cin, cout, ks, stride;
+  int map_mode, pad_mode, pad;
+  int src, resid, side, out;
+  int pre_relu, post_relu;
+  int transposed, tanh_out;
+};
+
+static LayerSpec L(const std::string& name, const std::string& wkey, const std::string& bkey,
+                   const std::string& gk, const std::string& bk, int cin, int cout, int ks, int stride,
+                   int map_mode, int pad_mode, int src, int resid, int side, int out, int pre_relu, int post_relu,
+                   int transposed = 0, int tanh_out = 0) {
+  LayerSpec s;
+  s.name = name; s.wkey = wkey; s.bkey = bkey; s.in_gkey = gk; s.in_bkey = bk;
+  s.cin = cin; s.cout = cout; s.ks = ks; s.stride = stride;
+  s.map_mode = map_mode; s.pad_mode = pad_mode; s.pad = (map_mode == MAP_ZERO_INSERT2) ? 1 : ks / 2;
+  s.src = src; s.resid = resid; s.side = side; s.out = out;
+  s.pre_relu = pre_relu; s.post_relu = post_relu; s.transposed = transposed; s.tanh_out = tanh_out;
+  return s;
+}
+
+// transformer_net.TransformerNet (transformer_net.py:4-41)
+static std::vector<LayerSpec> johnson_layers() {
+  std::vector<LayerSpec> v;
+  auto cw = [](const std::string& n) { return n + ".conv2d.weight"; };
+  auto cb = [](const std::string& n) { return n + ".conv2d.bias"; };
+  auto g = [](const std::string& n) { return n + ".weight"; };
+  auto b = [](const std::string& n) { return n + ".bias"; };
+  v.push_back(L("conv1", cw("conv1"), cb("conv1"), "", "", 3, 32, 9, 1, MAP_IDENTITY, PAD_REFLECT, BUF_IMAGE, -1, -1, B_R1, 0, 0));
+  v.push_back(L("conv2", cw("conv2"), cb("conv2"), g("in1"), b("in1"), 32, 64, 3, 2, MAP_IDENTITY, PAD_REFLECT, B_R1, -1, -1, B_R2, 1, 0));
+  v.push_back(L("conv3", cw("conv3"), cb("conv3"), g("in2"), b("in2"), 64, 128, 3, 2, MAP_IDENTITY, PAD_REFLECT, B_R2, -1, -1, B_T2, 1, 0));
+  std::string prev_g = g("in3"), prev_b = b("in3");
+  int ya = B_YA, yb = B_YB;
+  for (int i = 1; i <= 5; ++i) {
+    const std::string r = "res" + std::to_string(i);
+    // block input y = [relu](IN(prev raw)) [+ previous block input]; materialised into `ya`
+    v.push_back(L(r + ".conv1", cw(r + ".conv1"), cb(r + ".conv1"), prev_g, prev_b, 128, 128, 3, 1, MAP_IDENTITY, PAD_REFLECT,
+                  B_T2, i == 1 ? -1 : yb, ya, B_T1, i == 1 ? 1 : 0, 0));
+    v.push_back(L(r + ".conv2", cw(r + ".conv2"), cb(r + ".conv2"), g(r + ".in1"), b(r + ".in1"), 128, 128, 3, 1, MAP_IDENTITY, PAD_REFLECT,
+                  B_T1, -1, -1, B_T2, 1, 0));
+    prev_g = g(r + ".in2"); prev_b = b(r + ".in2");
+    std::swap(ya, yb);
+  }
+  v.push_back(L("deconv1", cw("deconv1"), cb("deconv1"), prev_g, prev_b, 128, 64, 3, 1, MAP_UP2, PAD_REFLECT, B_T2, yb, -1, B_R2, 0, 0));
+  v.push_back(L("deconv2", cw("deconv2"), cb("deconv2"), g("in4"), b("in4"), 64, 32, 3, 1, MAP_UP2, PAD_REFLECT, B_R2, -1, -1, B_R1, 1, 0));
+  v.push_back(L("deconv3", cw("deconv3"), cb("deconv3"), g("in5"), b("in5"), 32, 3, 9, 1, MAP_IDENTITY, PAD_REFLECT, B_R1, -1, -1, BUF_IMAGE, 1, 0));
+  return v;
+}
+
+// transformer_net_nst.TransformerNet (transformer_net_nst.py:62-127)
+static std::vector<LayerSpec> nst_layers() {
+  std::vector<LayerSpec> v;
+  auto nw = [](const std::string& n) { return n + ".norm.weight"; };
+  auto nb = [](const std::string& n) { return n + ".norm.bias"; };
+  v.push_back(L("down1", "down1.conv.weight", "down1.conv.bias", "", "", 3, 32, 9, 1, MAP_PREPAD_REFLECT, PAD_ZERO, BUF_IMAGE, -1, -1, B_R1, 0, 0));
+  v.push_back(L("down2", "down2.conv.weight", "down2.conv.bias", nw("down1"), nb("down1"), 32, 64, 3, 2, MAP_IDENTITY, PAD_ZERO, B_R1, -1, -1, B_R2, 1, 0));
+  v.push_back(L("down3", "down3.conv.weight", "down3.conv.bias", nw("down2"), nb("down2"), 64, 128, 3, 2, MAP_IDENTITY, PAD_ZERO, B_R2, -1, -1, B_T2, 1, 0));
+  std::string prev_g = nw("down3"), prev_b = nb("down3");
+  int ya = B_YA, yb = B_YB;
+  for (int i = 1; i <= 5; ++i) {
+    const std::string r = "res" + std::to_string(i);
+    v.push_back(L(r + ".conv1", r + ".conv1.weight", r + ".conv1.bias", prev_g, prev_b, 128, 128, 3, 1, MAP_IDENTITY, PAD_ZERO,
+                  B_T2, i == 1 ? -1 : yb, ya, B_T1, i == 1 ? 1 : 0, 0));
+    v.push_back(L(r + ".conv2", r + ".conv2.weight", r + ".conv2.bias", r + ".norm1.weight", r + ".norm1.bias", 128, 128, 3, 1,
+                  MAP_IDENTITY, PAD_ZERO, B_T1, -1, -1, B_T2, 1, 0));
+    prev_g = r + ".norm2.weight"; prev_b = r + ".norm2.bias";
+    std::swap(ya, yb);
+  }
+  v.push_back(L("up1", "up1.conv.weight", "up1.conv.bias", prev_g, prev_b, 128, 64, 3, 1, MAP_ZERO_INSERT2, PAD_ZERO, B_T2, yb, -1, B_R2, 0, 0, 1));
+  v.push_back(L("up2", "up2.conv.weight", "up2.conv.bias", nw("up1"), nb("up1"), 64, 32, 3, 1, MAP_ZERO_INSERT2, PAD_ZERO, B_R2, -1, -1, B_R1, 1, 0, 1));
+  v.push_back(L("final", "final.weight", "final.bias", nw("up2"), nb("up2"), 32, 3, 9, 1, MAP_IDENTITY, PAD_ZERO, B_R1, -1, -1, BUF_IMAGE, 1, 0));
+  return v;
+}
+
+// model.ReCoNet(frn=False) (model.py:75-116)
+static std::vector<LayerSpec> reconet_layers() {
+  std::vector<LayerSpec> v;
+  auto cw = [](const std::string& p) { return p + ".layers.0.layers.1.weight"; };
+  auto cb = [](const std::string& p) { return p + ".layers.0.layers.1.bias"; };
+  auto g = [](const std::string& p) { return p + ".layers.1.weight"; };
+  auto b = [](const std::string& p) { return p + ".layers.1.bias"; };
+  const std::string e0 = "encoder.layers.0", e1 = "encoder.layers.1", e2 = "encoder.layers.2";
+  v.push_back(L(e0, cw(e0), cb(e0), "", "", 3, 48, 9, 1, MAP_IDENTITY, PAD_REFLECT, BUF_IMAGE, -1, -1, B_R1, 0, 0));
+  v.push_back(L(e1, cw(e1), cb(e1), g(e0), b(e0), 48, 96, 3, 2, MAP_IDENTITY, PAD_REFLECT, B_R1, -1, -1, B_R2, 1, 0));
+  v.push_back(L(e2, cw(e2), cb(e2), g(e1), b(e1), 96, 192, 3, 2, MAP_IDENTITY, PAD_REFLECT, B_R2, -1, -1, B_T2, 1, 0));
+  std::string prev_g = g(e2), prev_b = b(e2);
+  int ya = B_YA, yb = B_YB;
+  for (int i = 3; i <= 6; ++i) {
+    const std::string r = "encoder.layers." + std::to_string(i);
+    const std::string b0 = r + ".branch.0", b1 = r + ".branch.1";
+    // ResLayer: x = relu(x + branch(x))  (model.py:57-60): the ReLU comes AFTER the add
+    v.push_back(L(b0, cw(b0), cb(b0), prev_g, prev_b, 192, 192, 3, 1, MAP_IDENTITY, PAD_REFLECT,
+                  B_T2, i == 3 ? -1 : yb, ya, B_T1, i == 3 ? 1 : 0, i == 3 ? 0 : 1));
+    v.push_back(L(b1, cw(b1), cb(b1), g(b0), b(b0), 192, 192, 3, 1, MAP_IDENTITY, PAD_REFLECT, B_T1, -1, -1, B_T2, 1, 0));
+    prev_g = g(b1); prev_b = b(b1);
+    std::swap(ya, yb);
+  }
+  const std::string d1 = "decoder.layers.1", d3 = "decoder.layers.3", d4 = "decoder.layers.4";
+  v.push_back(L(d1, cw(d1), cb(d1), prev_g, prev_b, 192, 96, 3, 1, MAP_UP2, PAD_REFLECT, B_T2, yb, -1, B_R2, 0, 1));
+  v.push_back(L(d3, cw(d3), cb(d3), g(d1), b(d1), 96, 48, 3, 1, MAP_UP2, PAD_REFLECT, B_R2, -1, -1, B_R1, 1, 0));
+  v.push_back(L(d4, d4 + ".layers.0.layers.1.weight", d4 + ".layers.0.layers.1.bias", g(d3), b(d3), 48, 3, 9, 1, MAP_IDENTITY,
+                PAD_REFLECT, B_R1, -1, -1, BUF_IMAGE, 1, 0, 0, 1));
+  return v;
+}
+
+// ---------------------------------------------------------------------------------------------
+// handle
+// ---------------------------------------------------------------------------------------------
+struct LayerDev {
+  float* wdir = nullptr;     // [ks*ks][cin][cout] fp32 (direct kernel)
+  void* wpack = nullptr;     // tcgen05 operand tiles (16-bit)
+  float* bias = nullptr;     // [cout]
+  float* in_gamma = nullptr; // [cin]
+  float* in_beta = nullptr;  // [cin]
+  TcPlan tc_static;          // shape-independent part of the tiling
+  bool tc_ok = false;
+};
+
+struct LayerPlan {
+  ConvParams p;              // pointers are filled per forward
+  TcPlan t;
+  bool use_tc = false;
+  int stats_off = 0;         // doubles, per micro-batch frame block
+  int src_stats_layer = -1;
+  double flops = 0, bytes = 0;
+};
+
+struct BufDims { int C = 0, H = 0, W = 0; size_t off = 0; size_t elems = 0; };
+
+struct nst_handle {
+  int device = 0, arch = 0, precision = 0, num_sms = 148;
+  std::vector<LayerSpec> specs;
+  std::vector<LayerDev> dev;
+  bool weights_loaded = false;
+  // plan cache
+  int plan_N = 0, plan_H = 0, plan_W = 0, plan_nb = 0;
+  int out_H = 0, out_W = 0;
+  std::vector<LayerPlan> plans;
+  BufDims bufs[NBUF];
+  size_t act_floats_per_frame = 0;
+  size_t stats_doubles_per_frame = 0;
+  size_t workspace_bytes = 0;
+  unsigned int* err_host = nullptr;
+  unsigned int* err_dev = nullptr;
+  long long launches = 0;
+  int microbatch = 8;
+  int dbg = 0;
+  unsigned long long tc_layer_mask = ~0ull;   // debug: bit i clear -> layer i runs on the direct kernel
+};
+
+static int ceil_div(int a, int b) { return (a + b - 1) / b; }
+static size_t round_up(size_t a, size_t b) { return (a + b - 1) / b * b; }
+
+// ---------------------------------------------------------------------------------------------
+// tcgen05 tiling
+// ---------------------------------------------------------------------------------------------
+static bool tc_supported(const LayerSpec& s) {
+  if (!(s.ks == 3 || s.ks == 9)) return false;
+  if (s.stride == 2 && s.ks != 3) return false;
+  if (s.stride != 1 && s.stride != 2) return false;
+  if (s.cin == 3) return s.ks == 9 && s.stride == 1;
+  if (s.cin % 16 != 0) return false;
+  if (s.cout != 3 && s.cout % 16 != 0) return false;
+  if (s.cout > 256) return false;
+  return true;
+}
+
+static void tc_plan_static(const LayerSpec& s, int precision, TcPlan& t) {
+  memset(&t, 0, sizeof(t));
+  t.NPAD = (int)round_up((size_t)s.cout, 16);
+  t.pair_mode = s.cin == 3;
+  if (t.pair_mode) {
+    t.CK = 8; t.planes = 1; t.nchunks = 1;
+    t.nent = s.ks * ((s.ks + 1) / 2);
+    t.k16_per_ent = 1;
+  } else {
+    t.CK = (s.cin % 32 == 0) ? 32 : 16;
+    t.planes = t.CK / 8;
+    t.nchunks = s.cin / t.CK;
+    t.nent = s.ks * s.ks;
+    t.k16_per_ent = t.CK / 16;
+  }
+  t.is_bf16 = precision == NST_PREC_BF16;
+  if (precision == NST_PREC_F16X3) { t.nterms = 3; t.a_tplanes = 2; t.b_tplanes = 2; }
+  else { t.nterms = 1; t.a_tplanes = 1; t.b_tplanes = 1; }
+  t.b_ent_bytes = (uint32_t)((t.pair_mode ? 2 : t.planes) * t.NPAD * 16);
+  int tg = (int)(8192 / (t.b_ent_bytes * t.b_tplanes));
+  tg = std::max(1, std::min(tg, t.nent));
+  if (s.ks == 9 && !t.pair_mode) tg = std::min(tg, 9);
+  t.tg = tg;
+  t.ngroups = ceil_div(t.nent, tg);
+  t.b_term_bytes = (uint32_t)tg * t.b_ent_bytes;
+  t.b_stage_bytes = t.b_term_bytes * (uint32_t)t.b_tplanes;
+  t.b_stages = t.b_stage_bytes <= 8192 ? 6 : (t.b_stage_bytes <= 16384 ? 4 : 2);
+  int mb = 256 / t.NPAD;                  // two accumulator buffers of MB*NPAD columns in 512
+  t.MB = std::max(1, std::min(mb, 8));
+}
+
+// Shape-dependent part: tile extent, halo buffer, shared-memory budget.
+static bool tc_plan_geometry(const ConvParams& p, TcPlan& t) {
+  const int e = p.ks - 1;
+  const int bar_bytes = 512;
+  for (int MB = t.MB; MB >= 1; MB = (MB > 1 ? MB / 2 : 0)) {
+    const int M = MB * 128;
+    const double mma_cyc = (double)MB * t.nchunks * t.nent * t.k16_per_ent * t.nterms * (t.NPAD / 2.0);
+    double best = 1e30;
+    int bTH = 0, bTW = 0, bP = 0;
+    for (int TH = 1; TH <= std::min(64, M); ++TH) {
+      int P = M / TH;
+      int TW = p.stride == 1 ? P - e : P - 1;
+      if (TW < 1) continue;
+      if (TW > p.Wo) { TW = p.Wo; P = p.stride == 1 ? TW + e : TW + 1; }
+      if (TW < 4 && p.Wo >= 4) continue;
+      const int THe = std::min(TH, p.Ho);
+      const double tiles = (double)ceil_div(p.Ho, THe) * ceil_div(p.Wo, TW);
+      const double halo = p.stride == 1 ? (double)(THe + e) * P : 4.0 * (THe + 1) * P;
+      const double prod_cyc = halo * t.planes * t.nchunks * 10.0;
+      const double cost = tiles * (std::max(mma_cyc, prod_cyc) + 0.15 * std::min(mma_cyc, prod_cyc) + 2000.0);
+      if (cost < best) { best = cost; bTH = THe; bTW = TW; bP = P; }
+    }
+    if (bTH == 0) continue;
+    t.TH = bTH; t.TW = bTW; t.P = bP;
+    const int Mused = ceil_div(bTH * bP, 128);
+    const int MBu = std::min(MB, std::max(1, Mused));
+    int max_off = 0;
+    if (p.stride == 1) {
+      t.halo_h = bTH + e; t.halo_w = bP; t.SUBPOS = 0;
+      int k = 0;
+      if (t.pair_mode) {
+        for (int r = 0; r < p.ks; ++r) for (int sp = 0; sp < (p.ks + 1) / 2; ++sp) t.ent_off[k++] = r * bP + 2 * sp;
+        max_off = e * bP + e + 1;
+      } else {
+        for (int r = 0; r < p.ks; ++r) for (int s = 0; s < p.ks; ++s) t.ent_off[k++] = r * bP + s;
+        max_off = e * bP + e;
+      }
+      t.NPOS = std::max(MBu * 128 + max_off + 2, t.halo_h * bP + 2);
+    } else {
+      t.halo_h = 2 * bTH + 1; t.halo_w = 2 * bTW + 1;
+      t.SUBPOS = (bTH + 1) * bP + 2;
+      int k = 0;
+      for (int r = 0; r < 3; ++r) for (int s = 0; s < 3; ++s) t.ent_off[k++] = ((r & 1) * 2 + (s & 1)) * t.SUBPOS + (r >> 1) * bP + (s >> 1);
+      max_off = 3 * t.SUBPOS + bP + 1;
+      t.NPOS = std::max(MBu * 128 + max_off + 2, 4 * t.SUBPOS);
+    }
+    // plane stride (in 16-byte units) chosen so the producers' 8-lane store phases cover all banks
+    if (t.planes == 4) { while (t.NPOS % 8 != 2) ++t.NPOS; }
+    else if (t.planes == 2) { while (t.NPOS % 8 != 4) ++t.NPOS; }
+    else { t.NPOS = (int)round_up((size_t)t.NPOS, 2); }
+    t.a_plane_bytes = (uint32_t)t.NPOS * 16u;
+    t.a_term_bytes = t.a_plane_bytes * (uint32_t)t.planes;
+    t.a_stage_bytes = (uint32_t)round_up((size_t)t.a_term_bytes * t.a_tplanes, 128);
+    const int b_total = t.b_stages * (int)t.b_stage_bytes;
+    const int avail = TC_SMEM_LIMIT - b_total - bar_bytes;
+    int a_stages = avail / (int)t.a_stage_bytes;
+    const int want = t.nchunks == 1 ? 2 : 3;
+    if (a_stages < 2 && MB > 1) continue;        // try a smaller tile
+    if (a_stages < 1) return false;
+    t.a_stages = std::min(a_stages, std::min(TC_MAX_A_STAGES, want + 1));
+    t.MB = MBu;
+    t.tiles_x = ceil_div(p.Wo, t.TW);
+    t.tiles_y = ceil_div(p.Ho, t.TH);
+    t.num_tiles = t.tiles_x * t.tiles_y * p.N;
+    t.smem_bytes = (uint32_t)(t.a_stages * t.a_stage_bytes + b_total + bar_bytes);
+    if (t.a_plane_bytes >= (1u << 18)) return false;
+    return true;
+  }
+  return false;
+}
+
+// Host packing of one layer's weights into the weight-stage images the kernel bulk-copies:
+// [chunk][group][term plane][entry in group][8-channel plane][NPAD][8] 16-bit.
+static std::vector<uint16_t> tc_pack_weights(const LayerSpec& s, const TcPlan& t, const std::vector<float>& w_oihw) {
+  const size_t stage_elems = t.b_stage_bytes / 2;
+  std::vector<uint16_t> out((size_t)t.nchunks * t.ngroups * stage_elems, 0);
+  auto conv16 = [&](float v) -> uint16_t {
+    if (t.is_bf16) { __nv_bfloat16 h = __float2bfloat16_rn(v); uint16_t u; memcpy(&u, &h, 2); return u; }
+    __half h = __float2half_rn(v); uint16_t u; memcpy(&u, &h, 2); return u;
+  };
+  auto back16 = [&](uint16_t u) -> float {
+    if (t.is_bf16) { __nv_bfloat16 h; memcpy(&h, &u, 2); return __bfloat162float(h); }
+    __half h; memcpy(&h, &u, 2); return __half2float(h);
+  };
+  const int ks = s.ks;
+  const int kplanes = t.pair_mode ? 2 : t.planes;
+  for (int ch = 0; ch < t.nchunks; ++ch) {
+    for (int ent = 0; ent < t.nent; ++ent) {
+      const int grp = ent / t.tg, e = ent % t.tg;
+      for (int kp = 0; kp < kplanes; ++kp) {
+        for (int n = 0; n < t.NPAD; ++n) {
+          for (int i = 0; i < 8; ++i) {
+            float v = 0.f;
+            if (n < s.cout) {
+              if (t.pair_mode) {
+                const int per_row = (ks + 1) / 2;
+                const int r = ent / per_row, sp = ent % per_row;
+                const int sx = 2 * sp + kp;
+                if (sx < ks && i < s.cin) v = w_oihw[(((size_t)n * s.cin + i) * ks + r) * ks + sx];
+              } else {
+                const int r = ent / ks, sx = ent % ks;
+                const int ci = ch * t.CK + kp * 8 + i;
+                v = w_oihw[(((size_t)n * s.cin + ci) * ks + r) * ks + sx];
+              }
+            }
+            const uint16_t hi = conv16(v);
+            const size_t base = ((size_t)ch * t.ngroups + grp) * stage_elems;
+            const size_t within = ((size_t)e * kplanes + kp) * t.NPAD * 8 + (size_t)n * 8 + i;
+            out[base + within] = hi;
+            if (t.b_tplanes == 2) out[base + t.b_term_bytes / 2 + within] = conv16(v - back16(hi));
+          }
+        }
+      }
+    }
+  }
+  return out;
+}
+
+// ---------------------------------------------------------------------------------------------
+// lifetime
+// ---------------------------------------------------------------------------------------------
+extern "C" const char* nst_last_error(void) { return g_err; }
+extern "C" const char* nst_version(void) { return "b200nst 0.1 (sm_100a, tcgen05 implicit-GEMM conv)"; }
+
+extern "C" int nst_create(int device, int arch, int precision, nst_handle** out) {
+  if (out == nullptr) return fail(NST_ERR_INVALID, "nst_create: out is null");
+  *out = nullptr;
+  if (arch < 0 || arch > 2) return fail(NST_ERR_INVALID, "nst_create: unknown arch %d", arch);
+  if (precision < 0 || precision > 3) return fail(NST_ERR_INVALID, "nst_create: unknown precision %d", precision);
+  int ndev = 0;
+  CUDA_TRY(cudaGetDeviceCount(&ndev));
+  if (device < 0 || device >= ndev) return fail(NST_ERR_CUDA, "nst_create: CUDA device %d not present (%d visible); there is no CPU path", device, ndev);
+  cudaDeviceProp prop;
+  CUDA_TRY(cudaGetDeviceProperties(&prop, device));
+  if (prop.major != 10) return fail(NST_ERR_CUDA, "nst_create: device %d is sm_%d%d; this library is built for sm_100a only", device, prop.major, prop.minor);
+  CUDA_TRY(cudaSetDevice(device));
+  nst_handle* h = new nst_handle();
+  h->device = device; h->arch = arch; h->precision = precision;
+  h->num_sms = prop.multiProcessorCount;
+  h->specs = arch == NST_ARCH_JOHNSON ? johnson_layers() : (arch == NST_ARCH_NST ? nst_layers() : reconet_layers());
+  h->dev.resize(h->specs.size());
+  if (const char* mbs = getenv("NST_MICROBATCH")) h->microbatch = std::max(1, atoi(mbs));
+  if (const char* d = getenv("NST_TC_DBG")) h->dbg = atoi(d);
+  if (const char* d = getenv("NST_TC_LAYER_MASK")) h->tc_layer_mask = strtoull(d, nullptr, 0);
+  cudaError_t e = cudaHostAlloc((void**)&h->err_host, sizeof(unsigned int), cudaHostAllocMapped);
+  if (e != cudaSuccess) { delete h; return fail(NST_ERR_CUDA, "cudaHostAlloc: %s", cudaGetErrorString(e)); }
+  *h->err_host = 0;
+  e = cudaHostGetDevicePointer((void**)&h->err_dev, h->err_host, 0);
+  if (e == cudaSuccess) e = conv_tc_init();
+  if (e != cudaSuccess) { cudaFreeHost(h->err_host); delete h; return fail(NST_ERR_CUDA, "nst_create: %s", cudaGetErrorString(e)); }
+  *out = h;
+  return NST_OK;
+}
+
+static void free_layer(LayerDev& d) {
+  cudaFree(d.wdir); cudaFree(d.wpack); cudaFree(d.bias); cudaFree(d.in_gamma); cudaFree(d.in_beta);
+  d = LayerDev();
+}
+
+extern "C" void nst_destroy(nst_handle* h) {
+  if (h == nullptr) return;
+  cudaSetDevice(h->device);
+  for (auto& d : h->dev) free_layer(d);
+  if (h->err_host) cudaFreeHost(h->err_host);
+  delete h;
+}
+
+template <typename T>
+static cudaError_t upload(T** dst, const std::vector<T>& src) {
+  cudaError_t e = cudaMalloc((void**)dst, std::max<size_t>(src.size(), 1) * sizeof(T));
+  if (e != cudaSuccess) return e;
+  return cudaMemcpy(*dst, src.data(), src.size() * sizeof(T), cudaMemcpyHostToDevice);
+}
+
+extern "C" int nst_load_weights(nst_handle* h, int n_tensors, const char* const* names, const float* const* ptrs,
+                                const int64_t* shapes, int* n_missing, int* n_unexpected) {
+  if (h == nullptr) return fail(NST_ERR_INVALID, "nst_load_weights: null handle");
+  CUDA_TRY(cudaSetDevice(h->device));
+  struct T { const float* p; int64_t s[4]; };
+  std::map<std::string, T> m;
+  for (int i = 0; i < n_tensors; ++i) {
+    T t; t.p = ptrs[i];
+    for (int k = 0; k < 4; ++k) t.s[k] = shapes[i * 4 + k];
+    m[names[i]] = t;
+  }
+  std::map<std::string, bool> used;
+  int missing = 0;
+  auto get = [&](const std::string& key, int64_t s0, int64_t s1, int64_t s2, int64_t s3, std::vector<float>& dst) -> int {
+    auto it = m.find(key);
+    if (it == m.end()) { ++missing; return fail(NST_ERR_WEIGHTS, "nst_load_weights: missing tensor '%s'", key.c_str()); }
+    const T& t = it->second;
+    if (t.s[0] != s0 || t.s[1] != s1 || t.s[2] != s2 || t.s[3] != s3)
+      return fail(NST_ERR_WEIGHTS, "nst_load_weights: '%s' has shape [%lld,%lld,%lld,%lld], expected [%lld,%lld,%lld,%lld]", key.c_str(),
+                  (long long)t.s[0], (long long)t.s[1], (long long)t.s[2], (long long)t.s[3], (long long)s0, (long long)s1, (long long)s2, (long long)s3);
+    used[key] = true;
+    dst.assign(t.p, t.p + (size_t)(s0 * s1 * s2 * s3));
+    return NST_OK;
+  };
+  for (size_t li = 0; li < h->specs.size(); ++li) {
+    const LayerSpec& s = h->specs[li];
+    LayerDev& d = h->dev[li];
+    free_layer(d);
+    std::vector<float> w_raw, w, bias, gam, bet;
+    int rc;
+    if (s.transposed) rc = get(s.wkey, s.cin, s.cout, s.ks, s.ks, w_raw);
+    else rc = get(s.wkey, s.cout, s.cin, s.ks, s.ks, w_raw);
+    if (rc != NST_OK) return rc;
+    if ((rc = get(s.bkey, s.cout, 1, 1, 1, bias)) != NST_OK) return rc;
+    // canonical OIHW of the equivalent direct convolution
+    w.resize((size_t)s.cout * s.cin * s.ks * s.ks);
+    if (s.transposed) {
+      // ConvTranspose2d(k3,s2,p1,op1) == conv over the zero-inserted input with the flipped kernel:
+      // W_eq[co][ci][r][s] = W_T[ci][co][k-1-r][k-1-s]
+      for (int co = 0; co < s.cout; ++co) for (int ci = 0; ci < s.cin; ++ci) for (int r = 0; r < s.ks; ++r) for (int q = 0; q < s.ks; ++q)
+        w[(((size_t)co * s.cin + ci) * s.ks + r) * s.ks + q] = w_raw[(((size_t)ci * s.cout + co) * s.ks + (s.ks - 1 - r)) * s.ks + (s.ks - 1 - q)];
+    } else {
+      w = w_raw;
+    }
+    std::vector<float> wdir((size_t)s.ks * s.ks * s.cin * s.cout);
+    for (int co = 0; co < s.cout; ++co) for (int ci = 0; ci < s.cin; ++ci) for (int r = 0; r < s.ks; ++r) for (int q = 0; q < s.ks; ++q)
+      wdir[((size_t)(r * s.ks + q) * s.cin + ci) * s.cout + co] = w[(((size_t)co * s.cin + ci) * s.ks + r) * s.ks + q];
+    CUDA_TRY(upload(&d.wdir, wdir));
+    CUDA_TRY(upload(&d.bias, bias));
+    if (!s.in_gkey.empty()) {
+      if ((rc = get(s.in_gkey, s.cin, 1, 1, 1, gam)) != NST_OK) return rc;
+      if ((rc = get(s.in_bkey, s.cin, 1, 1, 1, bet)) != NST_OK) return rc;
+      CUDA_TRY(upload(&d.in_gamma, gam));
+      CUDA_TRY(upload(&d.in_beta, bet));
+    }
+    d.tc_ok = h->precision != NST_PREC_FP32_DIRECT && tc_supported(s);
+    if (d.tc_ok) {
+      tc_plan_static(s, h->precision, d.tc_static);
+      d.tc_static.dbg = h->dbg;
+      std::vector<uint16_t> pk = tc_pack_weights(s, d.tc_static, w);
+      CUDA_TRY(upload((uint16_t**)&d.wpack, pk));
+    }
+  }
+  int unexpected = 0;
+  for (auto& kv : m) if (!used.count(kv.first)) ++unexpected;
+  if (n_missing) *n_missing = missing;
+  if (n_unexpected) *n_unexpected = unexpected;
+  CUDA_TRY(cudaDeviceSynchronize());
+  h->weights_loaded = true;
+  h->plan_N = 0;
+  return NST_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// planning
+// ---------------------------------------------------------------------------------------------
+static void out_shape(int arch, int H, int W, int* Ho, int* Wo) {
+  if (arch == NST_ARCH_NST) { *Ho = H; *Wo = W; return; }
+  *Ho = 4 * ceil_div(ceil_div(H, 2), 2);
+  *Wo = 4 * ceil_div(ceil_div(W, 2), 2);
+}
+
+extern "C" int nst_output_shape(const nst_handle* h, int H, int W, int* Ho, int* Wo) {
+  if (h == nullptr || Ho == nullptr || Wo == nullptr) return fail(NST_ERR_INVALID, "nst_output_shape: null argument");
+  out_shape(h->arch, H, W, Ho, Wo);
+  return NST_OK;
+}
+
+static int make_plan(nst_handle* h, int N, int H, int W) {
+  if (N < 1 || H < 1 || W < 1) return fail(NST_ERR_INVALID, "bad shape N=%d H=%d W=%d", N, H, W);
+  if (h->arch == NST_ARCH_NST && (H <= 40 || W <= 40))
+    return fail(NST_ERR_INVALID, "NST variant needs H,W > 40 (ReflectionPad2d(40), transformer_net_nst.py:74); got %dx%d", H, W);
+  if (h->arch != NST_ARCH_NST && (H < 5 || W < 5))
+    return fail(NST_ERR_INVALID, "input %dx%d too small for ReflectionPad2d(4)", H, W);
+  if (h->plan_N == N && h->plan_H == H && h->plan_W == W && !h->plans.empty()) return NST_OK;
+  const int nb = std::min(N, h->microbatch);
+  h->plans.assign(h->specs.size(), LayerPlan());
+  for (int b = 0; b < NBUF; ++b) h->bufs[b] = BufDims();
+  int producer[NBUF];
+  for (int b = 0; b < NBUF; ++b) producer[b] = -1;
+  size_t stats_off = 0;
+  for (size_t li = 0; li < h->specs.size(); ++li) {
+    const LayerSpec& s = h->specs[li];
+    LayerPlan& lp = h->plans[li];
+    ConvParams& p = lp.p;
+    memset(&p, 0, sizeof(p));
+    p.N = nb; p.Cin = s.cin; p.Cout = s.cout; p.ks = s.ks; p.stride = s.stride;
+    p.map_mode = s.map_mode; p.pad_mode = s.pad_mode; p.prepad = 40;
+    p.pad_t = p.pad_l = s.pad;
+    p.pre_relu = s.pre_relu; p.post_relu = s.post_relu; p.tanh_out = s.tanh_out;
+    p.blend = 1.f;
+    if (s.src == BUF_IMAGE) { p.Hs = H; p.Ws = W; }
+    else {
+      const BufDims& bd = h->bufs[s.src];
+      if (bd.C != s.cin) return fail(NST_ERR_STATE, "internal: layer %s expects %d channels, buffer has %d", s.name.c_str(), s.cin, bd.C);
+      p.Hs = bd.H; p.Ws = bd.W;
+      lp.src_stats_layer = producer[s.src];
+    }
+    p.in_inv_count = 1.0f / ((float)p.Hs * (float)p.Ws);
+    switch (s.map_mode) {
+      case MAP_UP2: case MAP_ZERO_INSERT2: p.Hc = 2 * p.Hs; p.Wc = 2 * p.Ws; break;
+      case MAP_PREPAD_REFLECT: p.Hc = p.Hs + 80; p.Wc = p.Ws + 80; break;
+      default: p.Hc = p.Hs; p.Wc = p.Ws;
+    }
+    int Hfull = (p.Hc + 2 * s.pad - s.ks) / s.stride + 1;
+    int Wfull = (p.Wc + 2 * s.pad - s.ks) / s.stride + 1;
+    if (s.pad_mode == PAD_REFLECT && (s.pad >= p.Hc || s.pad >= p.Wc))
+      return fail(NST_ERR_INVALID, "layer %s: reflection pad %d needs input larger than %dx%d", s.name.c_str(), s.pad, p.Hc, p.Wc);
+    p.Ho = Hfull; p.Wo = Wfull;
+    if (s.out == BUF_IMAGE) {
+      out_shape(h->arch, H, W, &h->out_H, &h->out_W);
+      if (h->arch == NST_ARCH_NST) {       // centre crop (transformer_net_nst.py:122-125)
+        p.oy_off = (Hfull - H) / 2; p.ox_off = (Wfull - W) / 2;
+        p.Ho = H; p.Wo = W;
+      } else if (Hfull != h->out_H || Wfull != h->out_W) {
+        return fail(NST_ERR_STATE, "internal: output %dx%d != expected %dx%d", Hfull, Wfull, h->out_H, h->out_W);
+      }
+    } else {
+      BufDims& bd = h->bufs[s.out];
+      bd.C = s.cout; bd.H = p.Ho; bd.W = p.Wo;
+      bd.elems = std::max(bd.elems, (size_t)s.cout * p.Ho * p.Wo);
+      producer[s.out] = (int)li;
+      lp.stats_off = (int)stats_off;
+      stats_off += (size_t)s.cout * 2;
+    }
+    if (s.side >= 0) {
+      BufDims& bd = h->bufs[s.side];
+      bd.C = s.cin; bd.H = p.Hs; bd.W = p.Ws;
+      bd.elems = std::max(bd.elems, (size_t)s.cin * p.Hs * p.Ws);
+    }
+    lp.flops = 2.0 * p.Ho * p.Wo * (double)s.cout * s.cin * s.ks * s.ks;      // per frame
+    lp.bytes = 4.0 * ((double)p.Hs * p.Ws * s.cin * (s.resid >= 0 ? 2 : 1) + (double)p.Ho * p.Wo * s.cout +
+                      (s.side >= 0 ? (double)p.Hs * p.Ws * s.cin : 0.0));
+    lp.use_tc = h->dev[li].tc_ok && ((h->tc_layer_mask >> li) & 1ull);
+    if (lp.use_tc) {
+      lp.t = h->dev[li].tc_static;
+      if (!tc_plan_geometry(p, lp.t)) lp.use_tc = false;
+    }
+  }
+  size_t off = 0;
+  for (int b = 0; b < NBUF; ++b) {
+    h->bufs[b].off = off;
+    off += round_up(h->bufs[b].elems, 64);
+  }
+  h->act_floats_per_frame = off;
+  h->stats_doubles_per_frame = stats_off;
+  h->workspace_bytes = round_up(off * sizeof(float) * nb, 256) + round_up(stats_off * sizeof(double) * nb, 256) + 256;
+  h->plan_N = N; h->plan_H = H; h->plan_W = W; h->plan_nb = nb;
+  return NST_OK;
+}
+
+extern "C" int nst_workspace_bytes(nst_handle* h, int N, int H, int W, size_t* bytes) {
+  if (h == nullptr || bytes == nullptr) return fail(NST_ERR_INVALID, "nst_workspace_bytes: null argument");
+  if (!h->weights_loaded) return fail(NST_ERR_STATE, "nst_workspace_bytes: call nst_load_weights first");
+  int rc = make_plan(h, N, H, W);
+  if (rc != NST_OK) return rc;
+  *bytes = h->workspace_bytes;
+  return NST_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// forward
+// ---------------------------------------------------------------------------------------------
+struct IoSpec {
+  int in_fmt, out_fmt;
+  const void* x; void* y;
+  float in_scale[3], in_shift[3], out_scale[3], out_shift[3];
+  int swap_rb; float blend; const float* mask; int composite_mode;
+};
+
+static int run_forward(nst_handle* h, const IoSpec& io, int N, int H, int W, void* workspace, size_t workspace_bytes,
+                       cudaStream_t stream, float* layer_ms) {
+  if (h == nullptr) return fail(NST_ERR_INVALID, "forward: null handle");
+  if (!h->weights_loaded) return fail(NST_ERR_STATE, "forward: call nst_load_weights first");
+  if (io.x == nullptr || io.y == nullptr) return fail(NST_ERR_INVALID, "forward: null tensor");
+  CUDA_TRY(cudaSetDevice(h->device));
+  int rc = make_plan(h, N, H, W);
+  if (rc != NST_OK) return rc;
+  if (workspace == nullptr || workspace_bytes < h->workspace_bytes)
+    return fail(NST_ERR_WORKSPACE, "forward: workspace %zu bytes < required %zu", workspace_bytes, h->workspace_bytes);
+  if (((uintptr_t)workspace & 255) != 0) return fail(NST_ERR_INVALID, "forward: workspace must be 256-byte aligned");
+  if (*h->err_host != 0) return fail(NST_ERR_CUDA, "forward: a previous kernel reported pipeline error 0x%08x", *h->err_host);
+  const int nb = h->plan_nb;
+  float* act = (float*)workspace;
+  double* stats = (double*)((char*)workspace + round_up(h->act_floats_per_frame * sizeof(float) * nb, 256));
+  const size_t stats_bytes = h->stats_doubles_per_frame * sizeof(double) * nb;
+  const int Ho = h->out_H, Wo = h->out_W;
+  const size_t in_px = (size_t)H * W * 3, out_px = (size_t)Ho * Wo * 3;
+  const size_t in_elt = io.in_fmt == IN_U8_NHWC3 ? 1 : 4, out_elt = io.out_fmt == OUT_U8_NHWC3 ? 1 : 4;
+  std::vector<cudaEvent_t> ev;
+  if (layer_ms) {
+    ev.resize(h->specs.size() + 1);
+    for (auto& e : ev) CUDA_TRY(cudaEventCreate(&e));
+    for (size_t i = 0; i < h->specs.size(); ++i) layer_ms[i] = 0.f;
+  }
+  for (int n0 = 0; n0 < N; n0 += nb) {
+    const int n = std::min(nb, N - n0);
+    CUDA_TRY(cudaMemsetAsync(stats, 0, stats_bytes, stream));
+    if (layer_ms) CUDA_TRY(cudaEventRecord(ev[0], stream));
+    for (size_t li = 0; li < h->specs.size(); ++li) {
+      const LayerSpec& s = h->specs[li];
+      const LayerDev& d = h->dev[li];
+      LayerPlan& lp = h->plans[li];
+      ConvParams p = lp.p;
+      p.N = n;
+      auto buf = [&](int b) -> float* { return act + h->bufs[b].off * nb; };
+      if (s.src == BUF_IMAGE) {
+        p.in_fmt = io.in_fmt;
+        p.src = (const char*)io.x + (size_t)n0 * in_px * in_elt;
+        for (int c = 0; c < 3; ++c) { p.in_scale[c] = io.in_scale[c]; p.in_shift[c] = io.in_shift[c]; }
+        p.swap_rb = io.swap_rb;
+      } else {
+        p.in_fmt = IN_F32_NHWC;
+        p.src = buf(s.src);
+        p.in_stats = stats + (size_t)h->plans[lp.src_stats_layer].stats_off * nb;
+        p.in_gamma = d.in_gamma; p.in_beta = d.in_beta;
+      }
+      p.resid = s.resid >= 0 ? buf(s.resid) : nullptr;
+      p.side_out = s.side >= 0 ? buf(s.side) : nullptr;
+      p.bias = d.bias;
+      if (s.out == BUF_IMAGE) {
+        p.out_fmt = io.out_fmt;
+        p.out = (char*)io.y + (size_t)n0 * out_px * out_elt;
+        for (int c = 0; c < 3; ++c) { p.out_scale[c] = io.out_scale[c]; p.out_shift[c] = io.out_shift[c]; }
+        p.swap_rb = io.swap_rb;
+        p.blend = io.blend; p.composite_mode = io.composite_mode;
+        p.mask = io.mask ? io.mask + (size_t)n0 * Ho * Wo : nullptr;
+        p.orig = (io.in_fmt == IN_U8_NHWC3 && (io.mask != nullptr || io.blend < 1.f)) ? (const uint8_t*)io.x + (size_t)n0 * in_px : nullptr;
+      } else {
+        p.out_fmt = OUT_F32_NHWC_STATS;
+        p.out = buf(s.out);
+        p.out_stats = stats + (size_t)lp.stats_off * nb;
+      }
+      // per-layer statistics tables are [nb][C][2]: stats_off counts doubles per frame
+      if (lp.use_tc) {
+        TcArgs a;
+        a.p = p; a.t = lp.t;
+        a.t.num_tiles = lp.t.tiles_x * lp.t.tiles_y * n;
+        a.wpack = d.wpack; a.err_flag = h->err_dev;
+        CUDA_TRY(launch_conv_tc(a, h->num_sms, stream));
+      } else {
+        CUDA_TRY(launch_conv_direct(p, d.wdir, stream));
+      }
+      ++h->launches;
+      if (layer_ms) CUDA_TRY(cudaEventRecord(ev[li + 1], stream));
+    }
+    if (layer_ms) {
+      CUDA_TRY(cudaStreamSynchronize(stream));
+      for (size_t li = 0; li < h->specs.size(); ++li) {
+        float ms = 0.f;
+        CUDA_TRY(cudaEventElapsedTime(&ms, ev[li], ev[li + 1]));
+        layer_ms[li] += ms;
+      }
+    }
+  }
+  if (layer_ms) for (auto& e : ev) cudaEventDestroy(e);
+  return NST_OK;
+}
+
+extern "C" int nst_forward_f32_nchw(nst_handle* h, const float* x, float* y, int N, int H, int W, void* workspace,
+                                    size_t workspace_bytes, void* stream) {
+  IoSpec io;
+  memset(&io, 0, sizeof(io));
+  io.in_fmt = IN_F32_NCHW3; io.out_fmt = OUT_F32_NCHW3; io.x = x; io.y = y;
+  for (int c = 0; c < 3; ++c) { io.in_scale[c] = 1.f; io.out_scale[c] = 1.f; }
+  io.blend = 1.f;
+  return run_forward(h, io, N, H, W, workspace, workspace_bytes, (cudaStream_t)stream, nullptr);
+}
+
+static int fill_u8_io(nst_handle* h, IoSpec& io, const uint8_t* x, uint8_t* y, int H, int W, const float in_scale[3],
+                      const float in_shift[3], const float out_scale[3], const float out_shift[3], int swap_rb, float blend,
+                      const float* mask, int composite_mode) {
+  if (h == nullptr) return fail(NST_ERR_INVALID, "forward_u8: null handle");
+  if (!in_scale || !in_shift || !out_scale || !out_shift) return fail(NST_ERR_INVALID, "forward_u8: null affine");
+  int Ho, Wo;
+  out_shape(h->arch, H, W, &Ho, &Wo);
+  if (Ho != H || Wo != W) return fail(NST_ERR_INVALID, "forward_u8: H,W must be multiples of 4 for this architecture (got %dx%d -> %dx%d)", H, W, Ho, Wo);
+  memset(&io, 0, sizeof(io));
+  io.in_fmt = IN_U8_NHWC3; io.out_fmt = OUT_U8_NHWC3; io.x = x; io.y = y;
+  for (int c = 0; c < 3; ++c) {
+    io.in_scale[c] = in_scale[c]; io.in_shift[c] = in_shift[c];
+    io.out_scale[c] = out_scale[c]; io.out_shift[c] = out_shift[c];
+  }
+  io.swap_rb = swap_rb; io.blend = blend; io.mask = mask; io.composite_mode = composite_mode;
+  return NST_OK;
+}
+
+extern "C" int nst_forward_u8_nhwc(nst_handle* h, const uint8_t* x, uint8_t* y, int N, int H, int W, const float in_scale[3],
+                                   const float in_shift[3], const float out_scale[3], const float out_shift[3], int swap_rb,
+                                   float blend, const float* mask, int composite_mode, void* workspace, size_t workspace_bytes,
+                                   void* stream) {
+  IoSpec io;
+  int rc = fill_u8_io(h, io, x, y, H, W, in_scale, in_shift, out_scale, out_shift, swap_rb, blend, mask, composite_mode);
+  if (rc != NST_OK) return rc;
+  return run_forward(h, io, N, H, W, workspace, workspace_bytes, (cudaStream_t)stream, nullptr);
+}
+
+extern "C" int nst_profile_layers_u8(nst_handle* h, const uint8_t* x, uint8_t* y, int N, int H, int W, void* workspace,
+                                     size_t workspace_bytes, void* stream, float* ms) {
+  if (ms == nullptr) return fail(NST_ERR_INVALID, "nst_profile_layers_u8: ms is null");
+  const float one[3] = {1.f, 1.f, 1.f}, zero[3] = {0.f, 0.f, 0.f}, inv[3] = {1.f / 255.f, 1.f / 255.f, 1.f / 255.f};
+  IoSpec io;
+  int rc = fill_u8_io(h, io, x, y, H, W, one, zero, inv, zero, 0, 1.f, nullptr, 0);
+  if (rc != NST_OK) return rc;
+  return run_forward(h, io, N, H, W, workspace, workspace_bytes, (cudaStream_t)stream, ms);
+}
+
+// ---------------------------------------------------------------------------------------------
+// introspection
+// ---------------------------------------------------------------------------------------------
+extern "C" int nst_num_layers(const nst_handle* h) { return h ? (int)h->specs.size() : 0; }
+
+extern "C" int nst_layer_info(const nst_handle* h, int layer, char* name, int name_cap, double* flops, double* bytes, int* kernel_kind) {
+  if (h == nullptr || layer < 0 || layer >= (int)h->specs.size()) return fail(NST_ERR_INVALID, "nst_layer_info: bad layer %d", layer);
+  if (h->plans.empty()) return fail(NST_ERR_STATE, "nst_layer_info: no plan yet (call nst_workspace_bytes or a forward)");
+  if (name && name_cap > 0) { strncpy(name, h->specs[layer].name.c_str(), name_cap - 1); name[name_cap - 1] = 0; }
+  if (flops) *flops = h->plans[layer].flops;
+  if (bytes) *bytes = h->plans[layer].bytes;
+  if (kernel_kind) *kernel_kind = h->plans[layer].use_tc ? 1 : 0;
+  return NST_OK;
+}
+
+extern "C" long long nst_launch_count(const nst_handle* h) { return h ? h->launches : 0; }
+
+// ---------------------------------------------------------------------------------------------
+// compositing
+// ---------------------------------------------------------------------------------------------
+static int composite_common(const void* const* srcs, int K, const void* original, const float* masks, int R, int J,
+                            const int* region_idx, const float* region_w, void* out, int H, int W, void* stream, bool u8) {
+  if (K < 1 || K > COMP_MAX_K || R < 1 || R > COMP_MAX_R || J < 1 || J > COMP_MAX_J)
+    return fail(NST_ERR_INVALID, "composite: need 1<=K<=%d, 1<=R<=%d, 1<=J<=%d (got K=%d R=%d J=%d)", COMP_MAX_K, COMP_MAX_R, COMP_MAX_J, K, R, J);
+  if (!srcs || !masks || !region_idx || !region_w || !out || H < 1 || W < 1) return fail(NST_ERR_INVALID, "composite: null / empty argument");
+  CompositeArgs a;
+  memset(&a, 0, sizeof(a));
+  for (int k = 0; k < K; ++k) { if (!srcs[k]) return fail(NST_ERR_INVALID, "composite: srcs[%d] is null", k); a.srcs[k] = srcs[k]; }
+  a.original = original; a.masks = masks; a.out = out; a.K = K; a.R = R; a.J = J; a.H = H; a.W = W;
+  for (int i = 0; i < R * J; ++i) {
+    if (region_idx[i] >= K || region_idx[i] < -1) return fail(NST_ERR_INVALID, "composite: region index %d out of range", region_idx[i]);
+    if (region_idx[i] == -1 && original == nullptr && region_w[i] != 0.f)
+      return fail(NST_ERR_INVALID, "composite: assignment includes original (-1) but no original frame provided");
+    a.idx[i] = region_idx[i]; a.w[i] = region_w[i];
+  }
+  CUDA_TRY(launch_composite(a, u8, (cudaStream_t)stream));
+  return NST_OK;
+}
+
+extern "C" int nst_composite_regions_u8(const uint8_t* const* srcs, int K, const uint8_t* original, const float* masks, int R, int J,
+                                        const int* region_idx, const float* region_w, uint8_t* out, int H, int W, void* stream) {
+  return composite_common((const void* const*)srcs, K, original, masks, R, J, region_idx, region_w, out, H, W, stream, true);
+}
+
+extern "C" int nst_composite_regions_f32(const float* const* srcs, int K, const float* original, const float* masks, int R, int J,
+                                         const int* region_idx, const float* region_w, float* out, int H, int W, void* stream) {
+  return composite_common((const void* const*)srcs, K, original, masks, R, J, region_idx, region_w, out, H, W, stream, false);
+}

@@ -1,0 +1,256 @@
+"""CPU oracle for the per-frame stylisation hot path.  TEST INFRASTRUCTURE ONLY.
+
+Only ``tests/``, ``__graft_entry__.smoke()`` and the ``cpu_baseline`` /
+``--impl reference`` legs of ``bench.py`` may import this module; the product
+path (``neuralstyletransferv1_b200``) never does.
+
+It is a plain ``torch.nn.functional`` fp32 restatement of the reference
+modules (which are themselves pure PyTorch; the arithmetic lives in the
+un-vendored, un-pinned ``torch`` dependency, ``requirements.txt:1`` -- here
+torch 2.11.0 CPU/oneDNN).  Each function cites the reference lines it follows.
+
+Parity pin: ``tests/golden/*.npz`` were produced by importing the REAL reference
+modules from ``/root/reference`` (``tests/golden/make_golden.py``); the oracle is
+checked against them in ``tests/test_oracle.py``.  The reference has no tests or
+golden vectors of its own for this path, so the pin is
+"reference executed in the build container", not "reference's own fixtures".
+"""
+from __future__ import annotations
+
+from typing import Dict, List, Optional, Sequence
+
+import torch
+import torch.nn.functional as F
+
+Tensor = torch.Tensor
+SD = Dict[str, Tensor]
+
+IMAGENET_MEAN = (0.485, 0.456, 0.406)   # pipeline.py:272
+IMAGENET_STD = (0.229, 0.224, 0.225)    # pipeline.py:273
+CAFFE_MEAN = (103.939, 116.779, 123.68)  # pipeline.py:1465
+
+
+# --------------------------------------------------------------------------- #
+# building blocks
+# --------------------------------------------------------------------------- #
+def _rconv(x: Tensor, w: Tensor, b: Tensor, stride: int = 1) -> Tensor:
+    """ReflectionPad2d(k//2) + Conv2d  (transformer_net.py:44-54, model.py:5-15)."""
+    p = w.shape[-1] // 2
+    return F.conv2d(F.pad(x, (p, p, p, p), mode="reflect"), w, b, stride=stride)
+
+
+def _inorm(x: Tensor, g: Tensor, b: Tensor) -> Tensor:
+    """InstanceNorm2d(affine=True), instance statistics in eval, eps 1e-5, biased var."""
+    return F.instance_norm(x, None, None, g, b, use_input_stats=True, eps=1e-5)
+
+
+def _up2(x: Tensor) -> Tensor:
+    """F.interpolate(mode='nearest', scale_factor=2)  (transformer_net.py:96)."""
+    return F.interpolate(x, scale_factor=2, mode="nearest")
+
+
+# --------------------------------------------------------------------------- #
+# transformer_net.TransformerNet  (transformer_net.py:4-41)
+# --------------------------------------------------------------------------- #
+def johnson_forward(sd: SD, x: Tensor) -> Tensor:
+    def conv(name, t, stride=1):
+        return _rconv(t, sd[name + ".conv2d.weight"], sd[name + ".conv2d.bias"], stride)
+
+    def norm(name, t):
+        return _inorm(t, sd[name + ".weight"], sd[name + ".bias"])
+
+    y = F.relu(norm("in1", conv("conv1", x)))                 # :30
+    y = F.relu(norm("in2", conv("conv2", y, 2)))              # :31
+    y = F.relu(norm("in3", conv("conv3", y, 2)))              # :32
+    for i in range(1, 6):                                     # :33-37, block :71-76
+        r = y
+        o = F.relu(norm(f"res{i}.in1", conv(f"res{i}.conv1", y)))
+        o = norm(f"res{i}.in2", conv(f"res{i}.conv2", o))
+        y = o + r                                             # no ReLU after the add
+    y = F.relu(norm("in4", conv("deconv1", _up2(y))))         # :38, :93-99
+    y = F.relu(norm("in5", conv("deconv2", _up2(y))))         # :39
+    return conv("deconv3", y)                                 # :40 raw output
+
+
+# --------------------------------------------------------------------------- #
+# transformer_net_nst.TransformerNet  (transformer_net_nst.py:62-127)
+# --------------------------------------------------------------------------- #
+def nst_forward(sd: SD, x: Tensor) -> Tensor:
+    h, w = x.shape[-2:]
+    y = F.pad(x, (40, 40, 40, 40), mode="reflect")            # :74,:100
+
+    def block(name, t, stride, pad):
+        t = F.conv2d(t, sd[name + ".conv.weight"], sd[name + ".conv.bias"], stride=stride, padding=pad)
+        return F.relu(_inorm(t, sd[name + ".norm.weight"], sd[name + ".norm.bias"]))
+
+    y = block("down1", y, 1, 4)                               # :77  (zero padding)
+    y = block("down2", y, 2, 1)                               # :78
+    y = block("down3", y, 2, 1)                               # :79
+    for i in range(1, 6):                                     # :82-86, block :28-43
+        r = y
+        o = F.conv2d(y, sd[f"res{i}.conv1.weight"], sd[f"res{i}.conv1.bias"], padding=1)
+        o = F.relu(_inorm(o, sd[f"res{i}.norm1.weight"], sd[f"res{i}.norm1.bias"]))
+        o = F.conv2d(o, sd[f"res{i}.conv2.weight"], sd[f"res{i}.conv2.bias"], padding=1)
+        o = _inorm(o, sd[f"res{i}.norm2.weight"], sd[f"res{i}.norm2.bias"])
+        y = o + r
+    for name in ("up1", "up2"):                               # :89-90, block :46-59
+        y = F.conv_transpose2d(y, sd[name + ".conv.weight"], sd[name + ".conv.bias"],
+                               stride=2, padding=1, output_padding=1)
+        y = F.relu(_inorm(y, sd[name + ".norm.weight"], sd[name + ".norm.bias"]))
+    y = F.conv2d(y, sd["final.weight"], sd["final.bias"], padding=4)   # :93
+    oh, ow = y.shape[-2:]
+    ch, cw = (oh - h) // 2, (ow - w) // 2                     # :122-125
+    return y[:, :, ch:ch + h, cw:cw + w]
+
+
+# --------------------------------------------------------------------------- #
+# model.ReCoNet(frn=False)  (model.py:75-116)
+# --------------------------------------------------------------------------- #
+def reconet_forward(sd: SD, x: Tensor) -> Tensor:
+    def cnl(prefix, t, stride=1, act=True):                   # ConvNormLayer model.py:18-40
+        t = _rconv(t, sd[prefix + ".layers.0.layers.1.weight"], sd[prefix + ".layers.0.layers.1.bias"], stride)
+        t = _inorm(t, sd[prefix + ".layers.1.weight"], sd[prefix + ".layers.1.bias"])
+        return F.relu(t) if act else t
+
+    y = cnl("encoder.layers.0", x)
+    y = cnl("encoder.layers.1", y, 2)
+    y = cnl("encoder.layers.2", y, 2)
+    for i in range(3, 7):                                     # ResLayer model.py:43-60
+        b = cnl(f"encoder.layers.{i}.branch.0", y)
+        b = cnl(f"encoder.layers.{i}.branch.1", b, act=False)
+        y = F.relu(y + b)                                     # ReLU AFTER the add
+    y = cnl("decoder.layers.1", _up2(y))
+    y = cnl("decoder.layers.3", _up2(y))
+    p = "decoder.layers.4.layers.0.layers.1"                  # ConvTanhLayer model.py:63-72
+    return torch.tanh(_rconv(y, sd[p + ".weight"], sd[p + ".bias"]))
+
+
+FORWARD = {"johnson": johnson_forward, "nst": nst_forward, "reconet": reconet_forward}
+
+
+def forward(arch: str, sd: SD, x: Tensor) -> Tensor:
+    with torch.no_grad():
+        return FORWARD[arch](sd, x.to(torch.float32))
+
+
+# --------------------------------------------------------------------------- #
+# io presets (pipeline.py:1447-1486), pack (pipeline.py:1943,2094; lib.py:46)
+# --------------------------------------------------------------------------- #
+def io_pre(x01: Tensor, preset: str) -> Tensor:
+    """x01: [N,3,H,W] fp32 in 0..1 -> network input."""
+    if preset == "tanh":
+        return x01 * 2.0 - 1.0
+    if preset == "imagenet_01":
+        m = torch.tensor(IMAGENET_MEAN).view(1, 3, 1, 1); s = torch.tensor(IMAGENET_STD).view(1, 3, 1, 1)
+        return (x01 - m) / s
+    if preset == "imagenet_255":
+        m = torch.tensor(IMAGENET_MEAN).view(1, 3, 1, 1); s = torch.tensor(IMAGENET_STD).view(1, 3, 1, 1)
+        return (x01 * 255.0 - m * 255.0) / (s * 255.0)
+    if preset == "caffe_bgr":
+        c = torch.tensor(CAFFE_MEAN).view(1, 3, 1, 1)
+        return (x01 * 255.0)[:, [2, 1, 0]] - c
+    if preset == "raw_01":
+        return x01
+    return x01 * 255.0  # raw_255 and the default branch
+
+
+def io_post(y: Tensor, preset: str) -> Tensor:
+    """network output -> out01 (clamped), pipeline.py:1451-1486."""
+    if preset == "tanh":
+        o = (y + 1.0) * 0.5
+    elif preset == "imagenet_01":
+        m = torch.tensor(IMAGENET_MEAN).view(1, 3, 1, 1); s = torch.tensor(IMAGENET_STD).view(1, 3, 1, 1)
+        o = y * s + m
+    elif preset == "caffe_bgr":
+        o = y[:, [2, 1, 0]] / 255.0
+    elif preset == "raw_01":
+        o = y
+    else:  # imagenet_255, raw_255, default
+        o = y / 255.0
+    return o.clamp(0, 1)
+
+
+def pack_u8(out01: Tensor) -> Tensor:
+    """ToPILImage semantics: (x*255).astype(uint8) == truncation; NCHW -> NHWC."""
+    return (out01.clamp(0, 1) * 255.0).to(torch.uint8).permute(0, 2, 3, 1).contiguous()
+
+
+def reconet_run_u8(sd: SD, images_u8_nhwc: Tensor) -> Tensor:
+    """lib.ReCoNetModel.run (lib.py:27-51) with utils.py:99-106."""
+    x = images_u8_nhwc.permute(0, 3, 1, 2).to(torch.float32) / 255
+    y = forward("reconet", sd, x * 2 - 1)
+    y = (y + 1) / 2
+    return torch.clamp(y * 255, 0, 255).to(torch.uint8).permute(0, 2, 3, 1).contiguous()
+
+
+def stylize_u8(arch: str, sd: SD, frames_u8_nhwc: Tensor, preset: str,
+               blend: float = 1.0, mask: Optional[Tensor] = None,
+               composite_mode: str = "keep") -> Tensor:
+    """Whole per-frame path of pipeline.py with uint8 in/out.
+
+    ToTensor (/255) -> io_pre -> model -> io_post -> optional mask composite
+    (pipeline.py:2040-2043) or uniform blend (pipeline.py:2089-2092) -> pack.
+    ``mask``: [N,H,W] fp32 alpha in 0..1 or None.
+    """
+    x01 = frames_u8_nhwc.permute(0, 3, 1, 2).to(torch.float32) / 255.0
+    out01 = io_post(forward(arch, sd, io_pre(x01, preset)), preset)
+    if out01.shape[-2:] != x01.shape[-2:]:
+        raise ValueError("oracle stylize_u8 expects H,W multiples of 4")
+    if mask is not None:
+        a = mask.unsqueeze(1)
+        if composite_mode == "keep":
+            out01 = (a * out01 + (1.0 - a) * x01).clamp(0, 1)
+        else:
+            out01 = ((1.0 - a) * out01 + a * x01).clamp(0, 1)
+    elif 0.0 <= blend < 1.0:
+        out01 = (blend * out01 + (1.0 - blend) * x01).clamp(0, 1)
+    return pack_u8(out01)
+
+
+# --------------------------------------------------------------------------- #
+# region compositing (region_blend.py:1049-1108, 1589-1679)
+# --------------------------------------------------------------------------- #
+def composite_regions(styled: Sequence[Tensor], masks: Sequence[Tensor], assignments: Sequence[int],
+                      original: Optional[Tensor] = None) -> Tensor:
+    """styled: list of [3,H,W] fp32 0..1; masks: list of [1,1,H,W]; -> [3,H,W]."""
+    C, H, W = styled[0].shape[-3:]
+    result = torch.zeros(1, C, H, W)
+    wsum = torch.zeros(1, 1, H, W)
+    for m, a in zip(masks, assignments):
+        src = original if a == -1 else styled[a]
+        src = src.reshape(1, C, H, W)
+        result += src * m.expand(1, C, H, W)
+        wsum += m
+    result = result / wsum.expand(1, C, H, W).clamp(min=1e-6)
+    return result.squeeze(0).clamp(0, 1)
+
+
+def composite_regions_advanced(styled: Sequence[Tensor], masks: Sequence[Tensor],
+                               model_indices: Sequence[Sequence[int]],
+                               model_weights: Sequence[Sequence[float]],
+                               original: Optional[Tensor] = None) -> Tensor:
+    """Single-scale form of region_blend.py:1589-1679 (per-region model blends)."""
+    C, H, W = styled[0].shape[-3:]
+    result = torch.zeros(1, C, H, W)
+    wsum = torch.zeros(1, 1, H, W)
+    for m, idxs, ws in zip(masks, model_indices, model_weights):
+        rb = torch.zeros(1, C, H, W)
+        for i, wt in zip(idxs, ws):
+            src = original if i == -1 else styled[i]
+            rb += wt * src.reshape(1, C, H, W)
+        result += rb * m.expand(1, C, H, W)
+        wsum += m
+    result = result / wsum.expand(1, C, H, W).clamp(min=1e-6)
+    return result.squeeze(0).clamp(0, 1)
+
+
+# --------------------------------------------------------------------------- #
+# metrics
+# --------------------------------------------------------------------------- #
+def u8_metrics(a_u8: Tensor, b_u8: Tensor):
+    """(max|delta|, PSNR dB) between two uint8 tensors -- the north_star tolerance."""
+    d = a_u8.to(torch.int16) - b_u8.to(torch.int16)
+    mx = int(d.abs().max())
+    mse = float((d.to(torch.float64) ** 2).mean())
+    psnr = float("inf") if mse == 0 else 10.0 * torch.log10(torch.tensor(255.0 ** 2 / mse)).item()
+    return mx, psnr

@@ -1,0 +1,123 @@
+"""Host logic and the C-ABI boundary, without a GPU."""
+import os
+import re
+import sys
+
+import pytest
+import torch
+
+from conftest import ROOT
+from neuralstyletransferv1_b200 import synth
+
+
+def test_cabi_exports_every_declared_symbol(built_lib):
+    hdr = open(os.path.join(ROOT, "include", "b200nst.h")).read()
+    declared = set(re.findall(r"\b(nst_[a-z0-9_]+)\s*\(", hdr))
+    assert len(declared) >= 15
+    from neuralstyletransferv1_b200 import _lib
+    assert declared == set(_lib.PROTOTYPES), "ctypes prototypes out of sync with include/b200nst.h"
+    for name in declared:
+        assert hasattr(built_lib, name), f"libb200nst.so does not export {name}"
+    assert b"sm_100a" in built_lib.nst_version()
+
+
+def test_create_fails_loudly_without_gpu(built_lib):
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    import ctypes as C
+    h = C.c_void_p()
+    rc = built_lib.nst_create(0, 0, 0, C.byref(h))
+    assert rc != 0 and not h.value
+    assert built_lib.nst_last_error()
+
+
+@pytest.mark.parametrize("arch,cls", [("johnson", "TransformerNet"), ("nst", "TransformerNetNST"), ("reconet", "ReCoNet")])
+def test_dropin_state_dict_surface(arch, cls):
+    import neuralstyletransferv1_b200 as m
+    model = getattr(m, cls)()
+    sd = synth.make_state_dict(arch, 0)
+    assert list(model.state_dict().keys()) == list(sd.keys())
+    for k, v in model.state_dict().items():
+        assert tuple(v.shape) == tuple(sd[k].shape), k
+    res = model.load_state_dict(sd, strict=True)
+    assert not res.missing_keys and not res.unexpected_keys
+    # legacy InstanceNorm buffers are dropped like pipeline.py:565-566 does
+    legacy = dict(sd)
+    first_norm = [k for k in sd if k.endswith(".weight") and sd[k].dim() == 1][0][:-len("weight")]
+    legacy[first_norm + "running_mean"] = torch.zeros(4)
+    legacy[first_norm + "running_var"] = torch.ones(4)
+    res = model.load_state_dict(legacy, strict=True)
+    assert not res.unexpected_keys
+    # strict=False returns (missing, unexpected) whose len() pipeline.py:569 prints
+    partial = {k: v for k, v in sd.items() if not k.startswith("res1") and "layers.3" not in k}
+    partial["bogus.weight"] = torch.zeros(1)
+    missing, unexpected = model.load_state_dict(partial, strict=False)
+    assert len(missing) > 0 and unexpected == ["bogus.weight"]
+    model.eval()
+    assert torch.equal(model.state_dict()[list(sd)[0]], sd[list(sd)[0]])
+
+
+def test_dropin_has_no_cpu_fallback():
+    import neuralstyletransferv1_b200 as m
+    model = m.TransformerNet()
+    with pytest.raises(RuntimeError, match="no CPU"):
+        model(torch.zeros(1, 3, 16, 16))
+    with pytest.raises(NotImplementedError):
+        m.ReCoNet(frn=True)
+
+
+def test_shims_resolve_like_pipeline_imports():
+    shim = os.path.join(ROOT, "neuralstyletransferv1_b200", "shims")
+    sys.path.insert(0, shim)
+    try:
+        for name in ("transformer_net", "transformer_net_nst", "lib"):
+            sys.modules.pop(name, None)
+        from transformer_net import TransformerNet as A            # pipeline.py:64
+        from transformer_net_nst import TransformerNet as B        # pipeline.py:69
+        from lib import ReCoNet as Cc                               # pipeline.py:50
+        assert A.ARCH == "johnson" and B.ARCH == "nst" and Cc.ARCH == "reconet"
+    finally:
+        sys.path.remove(shim)
+        for name in ("transformer_net", "transformer_net_nst", "lib"):
+            sys.modules.pop(name, None)
+
+
+@pytest.mark.parametrize("preset", ["raw_255", "raw_01", "tanh", "imagenet_01", "imagenet_255", "caffe_bgr"])
+def test_io_preset_affine_equals_oracle(preset):
+    from neuralstyletransferv1_b200 import io_preset_affine
+    from oracle import nst_oracle as O
+    s_in, b_in, s_out, b_out, swap = io_preset_affine(preset)
+    u8 = torch.arange(0, 256, dtype=torch.float32).view(1, 1, 16, 16).repeat(1, 3, 1, 1)
+    u8[:, 1] = u8[:, 1].flip(-1)
+    u8[:, 2] = (u8[:, 2] * 7) % 256
+    want_in = O.io_pre(u8 / 255.0, preset)
+    src = u8[:, [2, 1, 0]] if swap else u8
+    got_in = src * torch.tensor(s_in).view(1, 3, 1, 1) + torch.tensor(b_in).view(1, 3, 1, 1)
+    assert torch.allclose(got_in, want_in, rtol=1e-5, atol=1e-4)
+    y = torch.randn(1, 3, 16, 16) * 100 + 100
+    want_out = O.io_post(y, preset)
+    ysrc = y[:, [2, 1, 0]] if swap else y
+    got_out = (ysrc * torch.tensor(s_out).view(1, 3, 1, 1) + torch.tensor(b_out).view(1, 3, 1, 1)).clamp(0, 1)
+    assert torch.allclose(got_out, want_out, rtol=1e-5, atol=1e-6)
+
+
+def test_shard_ranges_partition_frames():
+    from neuralstyletransferv1_b200 import shard_range, shard_sizes
+    for n in (0, 1, 7, 64, 300):
+        for w in (1, 2, 3, 4, 8):
+            sizes = shard_sizes(n, w)
+            assert sum(sizes) == n and max(sizes) - min(sizes) <= 1
+            cover = []
+            for r in range(w):
+                a, b = shard_range(n, w, r)
+                cover += list(range(a, b))
+            assert cover == list(range(n))
+    with pytest.raises(ValueError):
+        shard_range(4, 2, 2)
+
+
+def test_synthetic_frames_are_deterministic():
+    a = synth.synthetic_frames_u8(3, 32, 48, seed=5)
+    b = synth.synthetic_frames_u8(3, 32, 48, seed=5)
+    assert a.dtype == torch.uint8 and tuple(a.shape) == (3, 32, 48, 3) and torch.equal(a, b)
+    assert int(a.max()) > 200 and int(a.min()) < 50
