@@ -131,6 +131,10 @@ int nst_layer_info(const nst_handle* h, int layer, char* name, int name_cap,
 int nst_profile_layers_u8(nst_handle* h, const uint8_t* x, uint8_t* y, int N, int H, int W,
                           void* workspace, size_t workspace_bytes, void* stream, float* ms);
 
+/* Host-only: write a human-readable table of the per-layer tiling the planner picks for this shape
+ * (one line per layer) into out[cap].  Needs no GPU. */
+int nst_describe_plan(int arch, int precision, int N, int H, int W, char* out, int cap);
+
 /* Number of kernels this library has launched on behalf of `h` since creation. */
 long long nst_launch_count(const nst_handle* h);
 

@@ -42,6 +42,7 @@ PROTOTYPES = {
                                  C.POINTER(C.c_double), C.POINTER(C.c_int)]),
     "nst_profile_layers_u8": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int,
                                         C.c_void_p, C.c_size_t, C.c_void_p, C.POINTER(C.c_float)]),
+    "nst_describe_plan": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_char_p, C.c_int]),
     "nst_launch_count": (C.c_longlong, [C.c_void_p]),
     "nst_last_error": (C.c_char_p, []),
     "nst_version": (C.c_char_p, []),
@@ -77,3 +78,11 @@ def check(rc: int, what: str) -> None:
     if rc != NST_OK:
         msg = load().nst_last_error()
         raise NstError(f"{what} failed (status {rc}): {msg.decode(errors='replace') if msg else ''}")
+
+
+def describe_plan(arch: str, precision: str, n: int, h: int, w: int) -> str:
+    """Planner dump for a shape (host only, no GPU)."""
+    import ctypes
+    buf = ctypes.create_string_buffer(16384)
+    check(load().nst_describe_plan(ARCH[arch], PRECISION[precision], n, h, w, buf, len(buf)), "nst_describe_plan")
+    return buf.value.decode()

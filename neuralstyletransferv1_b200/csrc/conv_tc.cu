@@ -143,12 +143,14 @@ __device__ __forceinline__ uint32_t make_idesc(int npad, int is_bf16) {
 }
 
 __device__ __forceinline__ uint32_t pack2(float a, float b, int is_bf16) {
+  uint32_t r;
   if (is_bf16) {
-    __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
-    return *reinterpret_cast<uint32_t*>(&h);
+    asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(b), "f"(a));
+  } else {
+    // saturate to +-65504 so an out-of-range activation can never become inf (inf * 0 = NaN in the MMA)
+    asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(b), "f"(a));
   }
-  __half2 h = __floats2half2_rn(a, b);
-  return *reinterpret_cast<uint32_t*>(&h);
+  return r;
 }
 __device__ __forceinline__ float2 unpack2(uint32_t u, int is_bf16) {
   if (is_bf16) return __bfloat1622float2(*reinterpret_cast<__nv_bfloat162*>(&u));
@@ -170,15 +172,11 @@ __device__ __forceinline__ TileCoord decode_tile(const TcPlan& t, int tile) {
 // ---------------------------------------------------------------------------------------------
 // operand producer: one (halo position, 8-channel group) item
 // ---------------------------------------------------------------------------------------------
-struct Item {
-  int q;            // slot in the plane, -1 = nothing to do
-  long long pix;    // source pixel index (n*Hs+sy)*Ws+sx, -1 = structural zero
-  long long side;   // side_out pixel index or -1
-};
+// Source-table entry of one halo slot: -1 = structural zero / filler, else the source pixel index
+// (n*Hs+sy)*Ws+sx (< 2^30), with bit 30 set when this tile owns the materialised ("side") value.
+constexpr int SIDE_BIT = 1 << 30;
 
-__device__ __forceinline__ Item locate(const ConvParams& p, const TcPlan& t, const TileCoord& tc, int q) {
-  Item it;
-  it.q = q; it.pix = -1; it.side = -1;
+__device__ __forceinline__ int locate(const ConvParams& p, const TcPlan& t, const TileCoord& tc, int q) {
   int hy, hx;
   bool filler = false;
   if (p.stride == 1) {
@@ -194,21 +192,23 @@ __device__ __forceinline__ Item locate(const ConvParams& p, const TcPlan& t, con
     hx = 2 * j + (sub & 1);
     filler = sub >= 4 || hy >= t.halo_h || hx >= t.halo_w;
   }
-  if (filler) return it;
+  if (filler) return -1;
   const int uy = (tc.ty0 + p.oy_off) * p.stride + hy - p.pad_t;
   const int ux = (tc.tx0 + p.ox_off) * p.stride + hx - p.pad_l;
   const int sy = map_coord(uy, p.Hc, p.Hs, p.map_mode, p.prepad, p.pad_mode);
   const int sx = map_coord(ux, p.Wc, p.Ws, p.map_mode, p.prepad, p.pad_mode);
-  if (sy < 0 || sx < 0) return it;
-  it.pix = ((long long)tc.n * p.Hs + sy) * p.Ws + sx;
+  if (sy < 0 || sx < 0) return -1;
+  int e = (tc.n * p.Hs + sy) * p.Ws + sx;
   if (p.side_out != nullptr) {
     // interior positions of this tile own the materialised value (identity-mapped stride-1 layers)
     const int iy = hy - p.pad_t, ix = hx - p.pad_l;
-    if (iy >= 0 && iy < t.TH && ix >= 0 && ix < t.TW && tc.ty0 + iy < p.Ho && tc.tx0 + ix < p.Wo) {
-      it.side = it.pix;   // uy == sy, ux == sx here
-    }
+    if (iy >= 0 && iy < t.TH && ix >= 0 && ix < t.TW && tc.ty0 + iy < p.Ho && tc.tx0 + ix < p.Wo) e |= SIDE_BIT;
   }
-  return it;
+  return e;
+}
+
+__device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
+  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -227,6 +227,8 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
   uint8_t* smem_b = smem_a + (size_t)t.a_stages * t.a_stage_bytes;
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem_b + (size_t)t.b_stages * t.b_stage_bytes);
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + NBARS);
+  int* srcpix = reinterpret_cast<int*>(tmem_slot + 4);                       // [NPOS] source table of the current tile
+  float2* coeff = reinterpret_cast<float2*>(srcpix + ((t.NPOS + 3) & ~3));    // [Cin] InstanceNorm (scale, shift) of sample n
 
   const uint32_t bar0 = smem_u32(bars);
   auto A_FULL = [&](int s) { return bar0 + 8u * (uint32_t)s; };
@@ -415,79 +417,94 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
     const int nitems = t.NPOS * planes;
     const int is_bf16 = t.is_bf16;
     const bool two = t.a_tplanes == 2;
+    const bool nhwc = p.in_fmt == IN_F32_NHWC;
+    const float lo1 = p.pre_relu ? 0.f : -INFINITY;
+    const float lo2 = p.post_relu ? 0.f : -INFINITY;
+    const float* __restrict__ srcf = (const float*)p.src;
+    const bool has_resid = p.resid != nullptr;
+    constexpr int U = 4;                    // items in flight per thread
     uint32_t sa = 0, pa = 0;
+    int cur_n = -1;
     for (int tile = first_tile; tile < t.num_tiles; tile += tile_step) {
       const TileCoord tc = decode_tile(t, tile);
+      named_bar_sync(1, TC_PROD_THREADS);          // every producer is done with the previous tile's tables
+      if (nhwc && tc.n != cur_n) {
+        for (int c = ptid; c < p.Cin; c += TC_PROD_THREADS) {
+          float s_, h_;
+          norm_coeff(p, tc.n, c, s_, h_);
+          coeff[c] = make_float2(s_, h_);
+        }
+        cur_n = tc.n;
+      }
+      for (int q = ptid; q < t.NPOS; q += TC_PROD_THREADS) srcpix[q] = locate(p, t, tc, q);
+      named_bar_sync(2, TC_PROD_THREADS);
       for (int ch = 0; ch < t.nchunks; ++ch) {
-        // InstanceNorm coefficients of this thread's 8 channels (previous layer's statistics)
-        float sc[8], sh[8];
         const int c0 = ch * t.CK + g * 8;
-        if (p.in_fmt == IN_F32_NHWC) {
+        float sc[8], sh[8];
+        if (nhwc) {
 #pragma unroll
-          for (int i = 0; i < 8; ++i) norm_coeff(p, tc.n, c0 + i, sc[i], sh[i]);
+          for (int i = 0; i < 8; ++i) { const float2 cf = coeff[c0 + i]; sc[i] = cf.x; sh[i] = cf.y; }
         }
         mbar_wait(A_EMPTY(sa), pa ^ 1u, err, 6);
         uint8_t* stage = smem_a + (size_t)sa * t.a_stage_bytes;
         uint8_t* plane_hi = stage + (size_t)g * t.a_plane_bytes;
         uint8_t* plane_lo = plane_hi + t.a_term_bytes;
 
-        for (int idx0 = ptid; idx0 < nitems; idx0 += 2 * TC_PROD_THREADS) {
-          // two items in flight per thread: issue all global loads before any use
-          Item itm[2];
-          float x[2][8];
+        for (int idx0 = ptid; idx0 < nitems; idx0 += U * TC_PROD_THREADS) {
+          int ent[U];
+          float x[U][8];
 #pragma unroll
-          for (int u = 0; u < 2; ++u) {
+          for (int u = 0; u < U; ++u) {
             const int idx = idx0 + u * TC_PROD_THREADS;
-            itm[u].q = -1; itm[u].pix = -1; itm[u].side = -1;
-            if (idx < nitems) itm[u] = locate(p, t, tc, idx >> pshift);
+            ent[u] = idx < nitems ? srcpix[idx >> pshift] : -2;       // -2: nothing to do
           }
-          if (p.in_fmt == IN_F32_NHWC) {
-            float4 a[2][2], r[2][2];
+          if (nhwc) {
+            float4 a[U][2], r[U][2];
 #pragma unroll
-            for (int u = 0; u < 2; ++u) {
+            for (int u = 0; u < U; ++u) {
               a[u][0] = a[u][1] = r[u][0] = r[u][1] = make_float4(0.f, 0.f, 0.f, 0.f);
-              if (itm[u].pix >= 0) {
-                const float4* s4 = reinterpret_cast<const float4*>((const float*)p.src + (size_t)itm[u].pix * p.Cin + c0);
+              if (ent[u] >= 0) {
+                const size_t off = (size_t)(ent[u] & (SIDE_BIT - 1)) * p.Cin + c0;
+                const float4* s4 = reinterpret_cast<const float4*>(srcf + off);
                 a[u][0] = __ldg(s4); a[u][1] = __ldg(s4 + 1);
-                if (p.resid != nullptr) {
-                  const float4* r4 = reinterpret_cast<const float4*>(p.resid + (size_t)itm[u].pix * p.Cin + c0);
+                if (has_resid) {
+                  const float4* r4 = reinterpret_cast<const float4*>(p.resid + off);
                   r[u][0] = __ldg(r4); r[u][1] = __ldg(r4 + 1);
                 }
               }
             }
 #pragma unroll
-            for (int u = 0; u < 2; ++u) {
+            for (int u = 0; u < U; ++u) {
               const float av[8] = {a[u][0].x, a[u][0].y, a[u][0].z, a[u][0].w, a[u][1].x, a[u][1].y, a[u][1].z, a[u][1].w};
               const float rv[8] = {r[u][0].x, r[u][0].y, r[u][0].z, r[u][0].w, r[u][1].x, r[u][1].y, r[u][1].z, r[u][1].w};
+              const bool live = ent[u] >= 0;
 #pragma unroll
               for (int i = 0; i < 8; ++i) {
-                float v = fmaf(av[i], sc[i], sh[i]);
-                if (p.pre_relu) v = fmaxf(v, 0.f);
-                v += rv[i];
-                if (p.post_relu) v = fmaxf(v, 0.f);
-                x[u][i] = (itm[u].pix >= 0) ? v : 0.f;
+                float v = fmaxf(fmaf(av[i], sc[i], sh[i]), lo1) + rv[i];
+                v = fmaxf(v, lo2);
+                x[u][i] = live ? v : 0.f;
               }
-              if (itm[u].side >= 0) {
-                float4* d4 = reinterpret_cast<float4*>(p.side_out + (size_t)itm[u].side * p.Cin + c0);
+              if (live && (ent[u] & SIDE_BIT)) {
+                float4* d4 = reinterpret_cast<float4*>(p.side_out + (size_t)(ent[u] & (SIDE_BIT - 1)) * p.Cin + c0);
                 d4[0] = make_float4(x[u][0], x[u][1], x[u][2], x[u][3]);
                 d4[1] = make_float4(x[u][4], x[u][5], x[u][6], x[u][7]);
               }
             }
           } else {
 #pragma unroll
-            for (int u = 0; u < 2; ++u) {
+            for (int u = 0; u < U; ++u) {
 #pragma unroll
               for (int i = 0; i < 8; ++i) x[u][i] = 0.f;
-              if (itm[u].pix >= 0) {
+              if (ent[u] >= 0) {
                 if (p.in_fmt == IN_F32_NCHW3) {
-                  // pix = (n*Hs+sy)*Ws+sx  ->  plane-separated address
-                  const long long hw = (long long)p.Hs * p.Ws;
-                  const long long n = itm[u].pix / hw;
-                  const long long rem = itm[u].pix - n * hw;
-                  const float* s = (const float*)p.src + (size_t)(n * 3 * hw + rem);
-                  x[u][0] = __ldg(s); x[u][1] = __ldg(s + hw); x[u][2] = __ldg(s + 2 * hw);
+                  // entry = (n*Hs+sy)*Ws+sx  ->  plane-separated address
+                  const int hw = p.Hs * p.Ws;
+                  const int n = ent[u] / hw;
+                  const int rem = ent[u] - n * hw;
+                  const float* s = srcf + ((size_t)n * 3 * hw + rem);
+                  x[u][0] = __ldg(s); x[u][1] = __ldg(s + hw); x[u][2] = __ldg(s + 2 * (size_t)hw);
                 } else {
-                  const uint8_t* s = (const uint8_t*)p.src + (size_t)itm[u].pix * 3;
+                  const uint8_t* s = (const uint8_t*)p.src + (size_t)ent[u] * 3;
                   const float b0 = (float)__ldg(s), b1 = (float)__ldg(s + 1), b2 = (float)__ldg(s + 2);
                   x[u][0] = (p.swap_rb ? b2 : b0) * p.in_scale[0] + p.in_shift[0];
                   x[u][1] = b1 * p.in_scale[1] + p.in_shift[1];
@@ -497,20 +514,22 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
             }
           }
 #pragma unroll
-          for (int u = 0; u < 2; ++u) {
-            if (itm[u].q < 0) continue;
-            uint32_t hi[4], lo[4];
+          for (int u = 0; u < U; ++u) {
+            if (ent[u] == -2) continue;
+            const int q = (idx0 + u * TC_PROD_THREADS) >> pshift;
+            uint32_t hi[4];
 #pragma unroll
-            for (int i = 0; i < 4; ++i) {
-              const float lim = 65504.f;
-              float v0 = x[u][2 * i], v1 = x[u][2 * i + 1];
-              if (!is_bf16) { v0 = fminf(fmaxf(v0, -lim), lim); v1 = fminf(fmaxf(v1, -lim), lim); }
-              hi[i] = pack2(v0, v1, is_bf16);
-              const float2 back = unpack2(hi[i], is_bf16);
-              lo[i] = pack2(v0 - back.x, v1 - back.y, is_bf16);
+            for (int i = 0; i < 4; ++i) hi[i] = pack2(x[u][2 * i], x[u][2 * i + 1], is_bf16);
+            *reinterpret_cast<uint4*>(plane_hi + (size_t)q * 16) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+            if (two) {
+              uint32_t lo[4];
+#pragma unroll
+              for (int i = 0; i < 4; ++i) {
+                const float2 back = unpack2(hi[i], is_bf16);
+                lo[i] = pack2(x[u][2 * i] - back.x, x[u][2 * i + 1] - back.y, is_bf16);
+              }
+              *reinterpret_cast<uint4*>(plane_lo + (size_t)q * 16) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
             }
-            *reinterpret_cast<uint4*>(plane_hi + (size_t)itm[u].q * 16) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
-            if (two) *reinterpret_cast<uint4*>(plane_lo + (size_t)itm[u].q * 16) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
           }
         }
         fence_proxy_async_smem();       // generic-proxy smem writes -> visible to tcgen05.mma (async proxy)

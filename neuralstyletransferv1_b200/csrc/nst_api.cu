@@ -259,8 +259,8 @@ static void tc_plan_static(const LayerSpec& s, int precision, TcPlan& t) {
 
 // Shape-dependent part: tile extent, halo buffer, shared-memory budget.
 static bool tc_plan_geometry(const ConvParams& p, TcPlan& t) {
+  if ((long long)p.N * p.Hs * p.Ws >= (1ll << 30)) return false;   // source-table entries are 30-bit pixel indices
   const int e = p.ks - 1;
-  const int bar_bytes = 512;
   for (int MB = t.MB; MB >= 1; MB = (MB > 1 ? MB / 2 : 0)) {
     const int M = MB * 128;
     const double mma_cyc = (double)MB * t.nchunks * t.nent * t.k16_per_ent * t.nterms * (t.NPAD / 2.0);
@@ -311,6 +311,8 @@ static bool tc_plan_geometry(const ConvParams& p, TcPlan& t) {
     t.a_term_bytes = t.a_plane_bytes * (uint32_t)t.planes;
     t.a_stage_bytes = (uint32_t)round_up((size_t)t.a_term_bytes * t.a_tplanes, 128);
     const int b_total = t.b_stages * (int)t.b_stage_bytes;
+    // barriers + TMEM slot + per-tile source table [NPOS] + per-sample norm coefficients [Cin<=256]
+    const int bar_bytes = 256 + (int)round_up((size_t)t.NPOS * 4, 16) + 256 * 8;
     const int avail = TC_SMEM_LIMIT - b_total - bar_bytes;
     int a_stages = avail / (int)t.a_stage_bytes;
     const int want = t.nchunks == 1 ? 2 : 3;
@@ -805,4 +807,49 @@ extern "C" int nst_composite_regions_u8(const uint8_t* const* srcs, int K, const
 extern "C" int nst_composite_regions_f32(const float* const* srcs, int K, const float* original, const float* masks, int R, int J,
                                          const int* region_idx, const float* region_w, float* out, int H, int W, void* stream) {
   return composite_common((const void* const*)srcs, K, original, masks, R, J, region_idx, region_w, out, H, W, stream, false);
+}
+
+// ---------------------------------------------------------------------------------------------
+// planner dump (no device needed): one line per layer with the tcgen05 tiling that would be used
+// ---------------------------------------------------------------------------------------------
+extern "C" int nst_describe_plan(int arch, int precision, int N, int H, int W, char* out, int cap) {
+  if (out == nullptr || cap < 1) return fail(NST_ERR_INVALID, "nst_describe_plan: no output buffer");
+  if (arch < 0 || arch > 2 || precision < 0 || precision > 3) return fail(NST_ERR_INVALID, "nst_describe_plan: bad arch/precision");
+  nst_handle h;
+  h.arch = arch; h.precision = precision;
+  h.specs = arch == NST_ARCH_JOHNSON ? johnson_layers() : (arch == NST_ARCH_NST ? nst_layers() : reconet_layers());
+  h.dev.resize(h.specs.size());
+  if (const char* mbs = getenv("NST_MICROBATCH")) h.microbatch = std::max(1, atoi(mbs));
+  for (size_t li = 0; li < h.specs.size(); ++li) {
+    h.dev[li].tc_ok = precision != NST_PREC_FP32_DIRECT && tc_supported(h.specs[li]);
+    if (h.dev[li].tc_ok) tc_plan_static(h.specs[li], precision, h.dev[li].tc_static);
+  }
+  int rc = make_plan(&h, N, H, W);
+  if (rc != NST_OK) return rc;
+  std::string s;
+  char line[512];
+  snprintf(line, sizeof(line), "arch=%d precision=%d N=%d (micro-batch %d) %dx%d -> %dx%d workspace=%.1f MB\n", arch, precision, N,
+           h.plan_nb, H, W, h.out_H, h.out_W, h.workspace_bytes / 1048576.0);
+  s += line;
+  for (size_t li = 0; li < h.specs.size(); ++li) {
+    const LayerSpec& sp = h.specs[li];
+    const LayerPlan& lp = h.plans[li];
+    const TcPlan& t = lp.t;
+    if (lp.use_tc) {
+      const double useful = (double)lp.p.Ho * lp.p.Wo / ((double)t.tiles_x * t.tiles_y * t.MB * 128);
+      snprintf(line, sizeof(line),
+               "%-28s %3d->%3d k%d s%d %4dx%-4d -> %4dx%-4d tc  TH=%2d TW=%3d P=%3d MB=%d NPOS=%4d CK=%2d chunks=%d ent=%2d tg=%d "
+               "A=%dx%uB B=%dx%uB smem=%uB tiles/img=%d rows_useful=%.2f GF=%.2f\n",
+               sp.name.c_str(), sp.cin, sp.cout, sp.ks, sp.stride, lp.p.Hs, lp.p.Ws, lp.p.Ho, lp.p.Wo, t.TH, t.TW, t.P, t.MB, t.NPOS,
+               t.CK, t.nchunks, t.nent, t.tg, t.a_stages, t.a_stage_bytes, t.b_stages, t.b_stage_bytes, t.smem_bytes,
+               t.tiles_x * t.tiles_y, useful, lp.flops * 1e-9);
+    } else {
+      snprintf(line, sizeof(line), "%-28s %3d->%3d k%d s%d %4dx%-4d -> %4dx%-4d direct GF=%.2f\n", sp.name.c_str(), sp.cin, sp.cout,
+               sp.ks, sp.stride, lp.p.Hs, lp.p.Ws, lp.p.Ho, lp.p.Wo, lp.flops * 1e-9);
+    }
+    s += line;
+  }
+  strncpy(out, s.c_str(), cap - 1);
+  out[cap - 1] = 0;
+  return NST_OK;
 }
