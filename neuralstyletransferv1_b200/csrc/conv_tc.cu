@@ -79,6 +79,11 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity, unsigne
   if (mbar_try_wait(bar, parity)) return;
   mbar_wait_slow(bar, parity, err, code);
 }
+__device__ __forceinline__ uint32_t elect_one_sync() {
+  uint32_t pred;
+  asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+  return pred;
+}
 __device__ __forceinline__ void fence_barrier_init() {
   asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
 }
@@ -274,54 +279,76 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
     }
   } else if (warp == 1) {
     // =========================== MMA issuer ===========================
-    if (lane == 0) {
+    // The whole warp walks the pipeline converged and one elected lane issues (the CUTLASS idiom):
+    // ptxas then keeps every descriptor in uniform registers.  Measured with tools/umma_bench.cu: a
+    // tcgen05.mma runs at its floor (64 cycles for M=128,N=128,K=16) only when the issuing loop costs
+    // less than that; building 64-bit descriptors from scratch per MMA in divergent code cost 170-370
+    // cycles per MMA.  So: descriptor high words are constants, low words are (addr>>4)|(LBO>>4)<<16
+    // and every step below is one 32-bit add in 16-byte units.
+    {
       const uint32_t idesc = make_idesc(t.NPAD, t.is_bf16);
-      const uint32_t a_lbo = t.pair_mode ? 16u : t.a_plane_bytes;
-      const uint32_t b_lbo = (uint32_t)t.NPAD * 16u;
-      const uint32_t a_kstep = 2u * t.a_plane_bytes;
-      const uint32_t b_kstep = 2u * (uint32_t)t.NPAD * 16u;
-      const uint32_t sa_base = smem_u32(smem_a);
-      const uint32_t sb_base = smem_u32(smem_b);
+      const uint32_t desc_hi = (128u >> 4) | (1u << 14);                      // SBO = 128 B, descriptor version 1
+      const uint32_t a_lbo16 = (t.pair_mode ? 16u : t.a_plane_bytes) >> 4;
+      const uint32_t a_lo_base = ((smem_u32(smem_a) >> 4) & 0x3FFFu) | (a_lbo16 << 16);
+      const uint32_t b_lo_base = ((smem_u32(smem_b) >> 4) & 0x3FFFu) | ((uint32_t)t.NPAD << 16);   // LBO = NPAD*16 B
+      const uint32_t a_kstep16 = (2u * t.a_plane_bytes) >> 4;
+      const uint32_t b_kstep16 = 2u * (uint32_t)t.NPAD;
+      const uint32_t a_stage16 = t.a_stage_bytes >> 4, b_stage16 = t.b_stage_bytes >> 4;
+      const uint32_t a_term16 = t.a_term_bytes >> 4, b_term16 = t.b_term_bytes >> 4, b_ent16 = t.b_ent_bytes >> 4;
+      const int MB = t.MB, NPAD = t.NPAD, k16 = t.k16_per_ent, nterms = t.nterms, tg = t.tg, nent = t.nent;
       uint32_t sa = 0, pa = 0, sb = 0, pb = 0, it = 0;
       for (int tile = first_tile; tile < t.num_tiles; tile += tile_step, ++it) {
         const uint32_t buf = it & 1u;
         mbar_wait(ACC_EMPTY(buf), ((it >> 1) & 1u) ^ 1u, err, 2);
         tc_fence_after();
-        const uint32_t tmem_acc = tmem_base + buf * (uint32_t)(t.MB * t.NPAD);
+        const uint32_t tmem_acc = tmem_base + buf * (uint32_t)(MB * NPAD);
+        uint32_t acc_on = 0u;
         for (int ch = 0; ch < t.nchunks; ++ch) {
           mbar_wait(A_FULL(sa), pa, err, 3);
           tc_fence_after();
-          const uint32_t a_stage = sa_base + sa * t.a_stage_bytes;
+          const uint32_t a_stage_lo = a_lo_base + sa * a_stage16;
+          int ent = 0;
           for (int g = 0; g < t.ngroups; ++g) {
             mbar_wait(B_FULL(sb), pb, err, 4);
             tc_fence_after();
-            const uint32_t b_stage = sb_base + sb * t.b_stage_bytes;
-            const int e_end = min(t.tg, t.nent - g * t.tg);
-            for (int e = 0; e < e_end; ++e) {
-              const int ent = g * t.tg + e;
-              const uint32_t a_ent = a_stage + (uint32_t)t.ent_off[ent] * 16u;
-              const uint32_t b_ent = b_stage + (uint32_t)e * t.b_ent_bytes;
-              for (int j = 0; j < t.k16_per_ent; ++j) {
-                for (int term = 0; term < t.nterms; ++term) {
-                  const uint32_t at = (term == 1) ? 1u : 0u;     // hi*hi, lo*hi, hi*lo
-                  const uint32_t bt = (term == 2) ? 1u : 0u;
-                  const uint64_t bdesc = make_desc(b_ent + bt * t.b_term_bytes + (uint32_t)j * b_kstep, b_lbo, 128u, t.dbg & 1);
-                  const uint32_t a_addr = a_ent + at * t.a_term_bytes + (uint32_t)j * a_kstep;
-                  const uint32_t acc_on = (ch | ent | j | term) != 0 ? 1u : 0u;
-                  for (int mb = 0; mb < t.MB; ++mb) {
-                    umma_f16(tmem_acc + (uint32_t)(mb * t.NPAD), make_desc(a_addr + (uint32_t)mb * 2048u, a_lbo, 128u, t.dbg & 1),
-                             bdesc, idesc, acc_on);
+            if (elect_one_sync()) {
+              uint32_t b_lo = b_lo_base + sb * b_stage16;
+              const int e_end = min(tg, nent - ent);
+              for (int e = 0; e < e_end; ++e, b_lo += b_ent16) {
+                const uint32_t a_lo = a_stage_lo + (uint32_t)t.ent_off[ent + e];
+                if (nterms == 1) {
+                  for (int j = 0; j < k16; ++j) {
+                    const uint64_t bdesc = ((uint64_t)desc_hi << 32) | (b_lo + (uint32_t)j * b_kstep16);
+                    const uint32_t a_j = a_lo + (uint32_t)j * a_kstep16;
+                    for (int mb = 0; mb < MB; ++mb)
+                      umma_f16(tmem_acc + (uint32_t)(mb * NPAD), ((uint64_t)desc_hi << 32) | (a_j + (uint32_t)mb * 128u), bdesc, idesc, acc_on);
+                    acc_on = 1u;
+                  }
+                } else {
+                  for (int j = 0; j < k16; ++j) {
+                    for (int term = 0; term < 3; ++term) {                      // hi*hi, lo*hi, hi*lo
+                      const uint64_t bdesc = ((uint64_t)desc_hi << 32) | (b_lo + (uint32_t)j * b_kstep16 + (term == 2 ? b_term16 : 0u));
+                      const uint32_t a_j = a_lo + (uint32_t)j * a_kstep16 + (term == 1 ? a_term16 : 0u);
+                      for (int mb = 0; mb < MB; ++mb)
+                        umma_f16(tmem_acc + (uint32_t)(mb * NPAD), ((uint64_t)desc_hi << 32) | (a_j + (uint32_t)mb * 128u), bdesc, idesc, acc_on);
+                      acc_on = 1u;
+                    }
                   }
                 }
               }
+              umma_commit(B_EMPTY(sb));
             }
-            umma_commit(B_EMPTY(sb));
+            __syncwarp();
+            acc_on = 1u;
+            ent += tg;
             if (++sb == (uint32_t)t.b_stages) { sb = 0; pb ^= 1u; }
           }
-          umma_commit(A_EMPTY(sa));
+          if (elect_one_sync()) umma_commit(A_EMPTY(sa));
+          __syncwarp();
           if (++sa == (uint32_t)t.a_stages) { sa = 0; pa ^= 1u; }
         }
-        umma_commit(ACC_FULL(buf));
+        if (elect_one_sync()) umma_commit(ACC_FULL(buf));
+        __syncwarp();
       }
     }
   } else if (warp < TC_FIRST_PROD_WARP) {
