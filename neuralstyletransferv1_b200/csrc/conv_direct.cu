@@ -19,10 +19,10 @@ __device__ __forceinline__ float fetch_in(const ConvParams& p, int n, int sy, in
                                           const float2* coeff) {
   if (p.in_fmt == IN_F32_NHWC) {
     const size_t idx = (((size_t)n * p.Hs + sy) * p.Ws + sx) * p.Cin + c;
-    float v = ((const float*)p.src)[idx];
+    float v = ld_act(p.src, idx, p.act16);
     if (p.in_stats != nullptr) v = v * coeff[c].x + coeff[c].y;
     if (p.pre_relu) v = fmaxf(v, 0.f);
-    if (p.resid != nullptr) v += p.resid[idx];
+    if (p.resid != nullptr) v += ld_act(p.resid, idx, p.act16);
     if (p.post_relu) v = fmaxf(v, 0.f);
     return v;
   }
@@ -55,7 +55,7 @@ conv_direct_kernel(const __grid_constant__ ConvParams p, const float* __restrict
   // materialise the transformed input (residual trunk) -- identity-mapped stride-1 layers only
   if (p.side_out != nullptr && valid) {
     for (int c = 0; c < p.Cin; ++c) {
-      p.side_out[(((size_t)n * p.Hs + oy) * p.Ws + ox) * p.Cin + c] = fetch_in(p, n, oy, ox, c, coeff);
+      st_act(p.side_out, (((size_t)n * p.Hs + oy) * p.Ws + ox) * p.Cin + c, fetch_in(p, n, oy, ox, c, coeff), p.act16);
     }
   }
 
@@ -84,9 +84,9 @@ conv_direct_kernel(const __grid_constant__ ConvParams p, const float* __restrict
     }
     if (p.out_fmt == OUT_F32_NHWC_STATS) {
       if (valid) {
-        float* o = (float*)p.out + (((size_t)n * p.Ho + oy) * p.Wo + ox) * p.Cout + co0;
+        const size_t o = (((size_t)n * p.Ho + oy) * p.Wo + ox) * p.Cout + co0;
 #pragma unroll
-        for (int j = 0; j < DIRECT_CO; ++j) if (co0 + j < p.Cout) o[j] = acc[j];
+        for (int j = 0; j < DIRECT_CO; ++j) if (co0 + j < p.Cout) st_act(p.out, o + j, acc[j], p.act16);
       }
 #pragma unroll
       for (int j = 0; j < DIRECT_CO; ++j) {

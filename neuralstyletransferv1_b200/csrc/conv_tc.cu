@@ -79,6 +79,31 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity, unsigne
   if (mbar_try_wait(bar, parity)) return;
   mbar_wait_slow(bar, parity, err, code);
 }
+// Debug instrumentation (NST_TC_PROF=1): cycles each role spends blocked on each barrier kind.
+struct WaitProf {
+  unsigned long long* buf;
+  long long acc[7];
+  long long t_start;
+  __device__ __forceinline__ void init(unsigned long long* b) {
+    buf = b;
+    if (buf) { for (int i = 0; i < 7; ++i) acc[i] = 0; t_start = clock64(); }
+  }
+  __device__ __forceinline__ void flush(int role, bool leader) {
+    if (buf && leader) {
+      for (int i = 1; i < 7; ++i) if (acc[i]) atomicAdd(buf + i, (unsigned long long)acc[i]);
+      atomicAdd(buf + 8 + role, (unsigned long long)(clock64() - t_start));
+    }
+  }
+};
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity, unsigned int* err, unsigned int code, WaitProf& wp) {
+  if (wp.buf) {
+    const long long t0 = clock64();
+    mbar_wait(bar, parity, err, code);
+    wp.acc[code] += clock64() - t0;
+  } else {
+    mbar_wait(bar, parity, err, code);
+  }
+}
 __device__ __forceinline__ uint32_t elect_one_sync() {
   uint32_t pred;
   asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
@@ -217,6 +242,224 @@ __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
 }
 
 // ---------------------------------------------------------------------------------------------
+// MMA issue: one weight stage (`n_ent` taps) against the current operand stage.  Descriptor low words
+// are (addr >> 4) | (LBO >> 4) << 16; every step is a 32-bit add in 16-byte units.  K16 / MB are
+// compile-time so the 2*K16*MB descriptors of a tap are straight-line uniform-register code.
+// ---------------------------------------------------------------------------------------------
+struct IssueArgs {
+  uint32_t tmem_acc, a_lo, b_lo, b_ent16, a_kstep16, b_kstep16, a_term16, b_term16, npad, idesc;
+  const uint32_t* ent_tab;
+  int n_ent;
+  uint32_t acc_on;
+};
+constexpr uint32_t DESC_HI = (128u >> 4) | (1u << 14);     // SBO = 128 B, descriptor version 1, SWIZZLE_NONE
+
+template <int K16, int MB>
+__device__ __forceinline__ void issue_group(const IssueArgs& a) {
+  uint32_t acc = a.acc_on;
+  uint32_t b_lo = a.b_lo;
+#pragma unroll 2
+  for (int e = 0; e < a.n_ent; ++e, b_lo += a.b_ent16) {
+    const uint32_t a_lo = a.a_lo + a.ent_tab[e];
+#pragma unroll
+    for (int j = 0; j < K16; ++j) {
+      const uint64_t bdesc = ((uint64_t)DESC_HI << 32) | (b_lo + (uint32_t)j * a.b_kstep16);
+#pragma unroll
+      for (int mb = 0; mb < MB; ++mb)
+        umma_f16(a.tmem_acc + (uint32_t)mb * a.npad, ((uint64_t)DESC_HI << 32) | (a_lo + (uint32_t)j * a.a_kstep16 + (uint32_t)mb * 128u), bdesc,
+                 a.idesc, acc);
+      acc = 1u;
+    }
+  }
+}
+
+__device__ __noinline__ void issue_group_generic(const IssueArgs& a, int k16, int MB, int nterms) {
+  uint32_t acc = a.acc_on;
+  uint32_t b_lo = a.b_lo;
+  for (int e = 0; e < a.n_ent; ++e, b_lo += a.b_ent16) {
+    const uint32_t a_lo = a.a_lo + a.ent_tab[e];
+    for (int j = 0; j < k16; ++j) {
+      for (int term = 0; term < nterms; ++term) {                      // hi*hi, lo*hi, hi*lo
+        const uint64_t bdesc = ((uint64_t)DESC_HI << 32) | (b_lo + (uint32_t)j * a.b_kstep16 + (term == 2 ? a.b_term16 : 0u));
+        const uint32_t a_j = a_lo + (uint32_t)j * a.a_kstep16 + (term == 1 ? a.a_term16 : 0u);
+        for (int mb = 0; mb < MB; ++mb)
+          umma_f16(a.tmem_acc + (uint32_t)mb * a.npad, ((uint64_t)DESC_HI << 32) | (a_j + (uint32_t)mb * 128u), bdesc, a.idesc, acc);
+        acc = 1u;
+      }
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// pipelined operand producer for fp16 NHWC activations (the default path of every layer but the first)
+// ---------------------------------------------------------------------------------------------
+// Each producer thread owns a fixed 8-channel plane g and the halo slots ptid/planes + k*(threads/planes);
+// its work is a flat sequence of batches (tile, channel chunk, batch-in-chunk) of PU slots.  The
+// global loads of batch i+1 are issued BEFORE batch i is transformed and written to shared memory,
+// across chunk and tile boundaries, so ~PU*16..32 B per thread are always in flight (the first version
+// waited for every batch: ncu showed the producers stalled on long_scoreboard ~45 % of the time).
+constexpr int PU = 4;
+
+template <bool HAS_RESID>
+struct ProdBatch {
+  int ent[PU];
+  uint4 a[PU];
+  uint4 r[HAS_RESID ? PU : 1];
+};
+
+struct ProdCursor {
+  int tile, ch, b;
+  uint32_t tb;         // which of the two source tables belongs to `tile`
+};
+
+template <bool HAS_RESID>
+__device__ __forceinline__ void prod_load(ProdBatch<HAS_RESID>& B, const ProdCursor& c, bool valid, const ConvParams& p, const TcPlan& t,
+                                          const int* srcpix, int tbl_stride, int ptid, int pshift, int g, int nitems) {
+  const __half* __restrict__ src = (const __half*)p.src;
+  const __half* __restrict__ res = (const __half*)p.resid;
+  const int* tbl = srcpix + c.tb * tbl_stride;
+  const int c0 = c.ch * t.CK + g * 8;
+#pragma unroll
+  for (int u = 0; u < PU; ++u) {
+    const int idx = ptid + (c.b * PU + u) * TC_PROD_THREADS;
+    B.ent[u] = (valid && idx < nitems) ? tbl[idx >> pshift] : -2;
+  }
+#pragma unroll
+  for (int u = 0; u < PU; ++u) {
+    B.a[u] = make_uint4(0u, 0u, 0u, 0u);
+    if (HAS_RESID) B.r[u] = make_uint4(0u, 0u, 0u, 0u);
+    if (B.ent[u] >= 0) {
+      const size_t off = (size_t)(B.ent[u] & (SIDE_BIT - 1)) * p.Cin + c0;
+      B.a[u] = __ldg(reinterpret_cast<const uint4*>(src + off));
+      if (HAS_RESID) B.r[u] = __ldg(reinterpret_cast<const uint4*>(res + off));
+    }
+  }
+}
+
+template <bool HAS_RESID>
+__device__ void produce_act16(const ConvParams& p, const TcPlan& t, uint8_t* smem_a, int* srcpix, float2* coeff, uint32_t bar_a_full0,
+                              uint32_t bar_a_empty0, unsigned int* err, unsigned long long* prof, int first_tile, int tile_step, int ptid) {
+  const int planes = t.planes;
+  const int pshift = planes == 4 ? 2 : (planes == 2 ? 1 : 0);
+  const int g = ptid & (planes - 1);
+  const int nitems = t.NPOS * planes;
+  const int tbl_stride = (t.NPOS + 3) & ~3;
+  const int nB = (nitems + PU * TC_PROD_THREADS - 1) / (PU * TC_PROD_THREADS);     // batches per chunk
+  const int is_bf16 = t.is_bf16;
+  const float lo1 = p.pre_relu ? 0.f : -INFINITY;
+  const float lo2 = p.post_relu ? 0.f : -INFINITY;
+  __half* side = (__half*)p.side_out;
+
+  auto build_table = [&](int tile, uint32_t tb) {
+    if (tile >= t.num_tiles) return;
+    const TileCoord tc = decode_tile(t, tile);
+    int* tbl = srcpix + tb * tbl_stride;
+    for (int q = ptid; q < t.NPOS; q += TC_PROD_THREADS) tbl[q] = locate(p, t, tc, q);
+  };
+  auto advance = [&](ProdCursor& c) {
+    if (++c.b == nB) {
+      c.b = 0;
+      if (++c.ch == t.nchunks) { c.ch = 0; c.tile += tile_step; c.tb ^= 1u; }
+    }
+  };
+
+  uint32_t sa = 0, pa = 0;
+  int cur_n = -1;
+  float sc[8], sh[8];
+  uint8_t* plane_hi = smem_a;
+  WaitProf wprof; wprof.init(prof);
+
+  // tile start: everyone is done with the table of the previous tile -> build the next tile's (it is
+  // first read by the prefetch that follows), refresh the per-sample norm coefficients
+  auto tile_begin = [&](const ProdCursor& c) {
+    if (c.b != 0 || c.ch != 0) return;
+    named_bar_sync(1, TC_PROD_THREADS);
+    const int n = c.tile / (t.tiles_x * t.tiles_y);
+    if (n != cur_n) {
+      for (int ch = ptid; ch < p.Cin; ch += TC_PROD_THREADS) {
+        float s_, h_;
+        norm_coeff(p, n, ch, s_, h_);
+        coeff[ch] = make_float2(s_, h_);
+      }
+      cur_n = n;
+    }
+    build_table(c.tile + tile_step, c.tb ^ 1u);
+    named_bar_sync(2, TC_PROD_THREADS);
+  };
+  auto process = [&](const ProdBatch<HAS_RESID>& B, const ProdCursor& c) {
+    if (c.b == 0) {
+      const int c0 = c.ch * t.CK + g * 8;
+#pragma unroll
+      for (int i = 0; i < 8; ++i) { const float2 cf = coeff[c0 + i]; sc[i] = cf.x; sh[i] = cf.y; }
+      mbar_wait(bar_a_empty0 + 8u * sa, pa ^ 1u, err, 6, wprof);
+      plane_hi = smem_a + (size_t)sa * t.a_stage_bytes + (size_t)g * t.a_plane_bytes;
+    }
+    const int c0 = c.ch * t.CK + g * 8;
+#pragma unroll
+    for (int u = 0; u < PU; ++u) {
+      const int e = B.ent[u];
+      if (e == -2) continue;
+      const int q = (ptid + (c.b * PU + u) * TC_PROD_THREADS) >> pshift;
+      uint32_t hi[4] = {0u, 0u, 0u, 0u};
+      if (e >= 0) {
+        const uint32_t aw[4] = {B.a[u].x, B.a[u].y, B.a[u].z, B.a[u].w};
+        uint32_t rw[4] = {0u, 0u, 0u, 0u};
+        if (HAS_RESID) { rw[0] = B.r[u].x; rw[1] = B.r[u].y; rw[2] = B.r[u].z; rw[3] = B.r[u].w; }
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const float2 av = unpack2(aw[i], 0);
+          float v0 = fmaxf(fmaf(av.x, sc[2 * i], sh[2 * i]), lo1);
+          float v1 = fmaxf(fmaf(av.y, sc[2 * i + 1], sh[2 * i + 1]), lo1);
+          if (HAS_RESID) { const float2 rv = unpack2(rw[i], 0); v0 += rv.x; v1 += rv.y; }
+          v0 = fmaxf(v0, lo2); v1 = fmaxf(v1, lo2);
+          hi[i] = pack2(v0, v1, is_bf16);
+        }
+        if (e & SIDE_BIT) {
+          // the materialised block input is stored as fp16 -- the same rounding the MMA operand gets
+          uint32_t sv[4];
+          if (is_bf16) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) { const float2 f = unpack2(hi[i], 1); sv[i] = pack2(f.x, f.y, 0); }
+          } else {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) sv[i] = hi[i];
+          }
+          *reinterpret_cast<uint4*>(side + (size_t)(e & (SIDE_BIT - 1)) * p.Cin + c0) = make_uint4(sv[0], sv[1], sv[2], sv[3]);
+        }
+      }
+      *reinterpret_cast<uint4*>(plane_hi + (size_t)q * 16) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+    }
+    if (c.b == nB - 1) {
+      fence_proxy_async_smem();
+      mbar_arrive(bar_a_full0 + 8u * sa);
+      if (++sa == (uint32_t)t.a_stages) { sa = 0; pa ^= 1u; }
+    }
+  };
+
+  ProdCursor cur;
+  cur.tile = first_tile; cur.ch = 0; cur.b = 0; cur.tb = 0u;
+  build_table(first_tile, 0u);
+  named_bar_sync(2, TC_PROD_THREADS);
+  ProdBatch<HAS_RESID> B0, B1;
+  prod_load<HAS_RESID>(B0, cur, cur.tile < t.num_tiles, p, t, srcpix, tbl_stride, ptid, pshift, g, nitems);
+  while (cur.tile < t.num_tiles) {
+    ProdCursor nxt = cur;
+    advance(nxt);
+    tile_begin(cur);
+    prod_load<HAS_RESID>(B1, nxt, nxt.tile < t.num_tiles, p, t, srcpix, tbl_stride, ptid, pshift, g, nitems);
+    process(B0, cur);
+    cur = nxt;
+    if (cur.tile >= t.num_tiles) break;
+    advance(nxt);
+    tile_begin(cur);
+    prod_load<HAS_RESID>(B0, nxt, nxt.tile < t.num_tiles, p, t, srcpix, tbl_stride, ptid, pshift, g, nitems);
+    process(B1, cur);
+    cur = nxt;
+  }
+  wprof.flush(3, ptid == 0);
+}
+
+// ---------------------------------------------------------------------------------------------
 // the kernel
 // ---------------------------------------------------------------------------------------------
 constexpr int NBARS = 2 * TC_MAX_A_STAGES + 2 * TC_MAX_B_STAGES + 4;
@@ -232,8 +475,9 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
   uint8_t* smem_b = smem_a + (size_t)t.a_stages * t.a_stage_bytes;
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem_b + (size_t)t.b_stages * t.b_stage_bytes);
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + NBARS);
-  int* srcpix = reinterpret_cast<int*>(tmem_slot + 4);                       // [NPOS] source table of the current tile
-  float2* coeff = reinterpret_cast<float2*>(srcpix + ((t.NPOS + 3) & ~3));    // [Cin] InstanceNorm (scale, shift) of sample n
+  uint32_t* ent_tab = tmem_slot + 4;                                         // [TC_MAX_ENT rounded to 84] tap offsets (MMA warp)
+  int* srcpix = reinterpret_cast<int*>(ent_tab + 84);                       // [NPOS] source table of the current tile
+  float2* coeff = reinterpret_cast<float2*>(srcpix + 2 * ((t.NPOS + 3) & ~3));  // [Cin] InstanceNorm (scale, shift) of sample n (two source tables before it)
 
   const uint32_t bar0 = smem_u32(bars);
   auto A_FULL = [&](int s) { return bar0 + 8u * (uint32_t)s; };
@@ -264,18 +508,20 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
   if (warp == 0) {
     // =========================== weight loader ===========================
     if (lane == 0) {
+      WaitProf wprof; wprof.init(args.prof);
       uint32_t sb = 0, pb = 0;
       const uint8_t* wp = reinterpret_cast<const uint8_t*>(args.wpack);
       const int nstage_per_tile = t.nchunks * t.ngroups;
       for (int tile = first_tile; tile < t.num_tiles; tile += tile_step) {
         for (int g = 0; g < nstage_per_tile; ++g) {
-          mbar_wait(B_EMPTY(sb), pb ^ 1u, err, 1);
+          mbar_wait(B_EMPTY(sb), pb ^ 1u, err, 1, wprof);
           mbar_arrive_expect_tx(B_FULL(sb), t.b_stage_bytes);
           bulk_g2s(smem_u32(smem_b + (size_t)sb * t.b_stage_bytes), wp + (size_t)g * t.b_stage_bytes,
                    t.b_stage_bytes, B_FULL(sb));
           if (++sb == (uint32_t)t.b_stages) { sb = 0; pb ^= 1u; }
         }
       }
+      wprof.flush(0, true);
     }
   } else if (warp == 1) {
     // =========================== MMA issuer ===========================
@@ -287,7 +533,6 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
     // and every step below is one 32-bit add in 16-byte units.
     {
       const uint32_t idesc = make_idesc(t.NPAD, t.is_bf16);
-      const uint32_t desc_hi = (128u >> 4) | (1u << 14);                      // SBO = 128 B, descriptor version 1
       const uint32_t a_lbo16 = (t.pair_mode ? 16u : t.a_plane_bytes) >> 4;
       const uint32_t a_lo_base = ((smem_u32(smem_a) >> 4) & 0x3FFFu) | (a_lbo16 << 16);
       const uint32_t b_lo_base = ((smem_u32(smem_b) >> 4) & 0x3FFFu) | ((uint32_t)t.NPAD << 16);   // LBO = NPAD*16 B
@@ -296,45 +541,40 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
       const uint32_t a_stage16 = t.a_stage_bytes >> 4, b_stage16 = t.b_stage_bytes >> 4;
       const uint32_t a_term16 = t.a_term_bytes >> 4, b_term16 = t.b_term_bytes >> 4, b_ent16 = t.b_ent_bytes >> 4;
       const int MB = t.MB, NPAD = t.NPAD, k16 = t.k16_per_ent, nterms = t.nterms, tg = t.tg, nent = t.nent;
+      WaitProf wprof; wprof.init(args.prof);
+      // tap -> A position offset table in shared memory (a uniform LDS per tap instead of an indexed constant load)
+      for (int i = lane; i < t.nent; i += 32) ent_tab[i] = (uint32_t)t.ent_off[i];
+      __syncwarp();
       uint32_t sa = 0, pa = 0, sb = 0, pb = 0, it = 0;
       for (int tile = first_tile; tile < t.num_tiles; tile += tile_step, ++it) {
         const uint32_t buf = it & 1u;
-        mbar_wait(ACC_EMPTY(buf), ((it >> 1) & 1u) ^ 1u, err, 2);
+        mbar_wait(ACC_EMPTY(buf), ((it >> 1) & 1u) ^ 1u, err, 2, wprof);
         tc_fence_after();
         const uint32_t tmem_acc = tmem_base + buf * (uint32_t)(MB * NPAD);
         uint32_t acc_on = 0u;
         for (int ch = 0; ch < t.nchunks; ++ch) {
-          mbar_wait(A_FULL(sa), pa, err, 3);
+          mbar_wait(A_FULL(sa), pa, err, 3, wprof);
           tc_fence_after();
           const uint32_t a_stage_lo = a_lo_base + sa * a_stage16;
           int ent = 0;
           for (int g = 0; g < t.ngroups; ++g) {
-            mbar_wait(B_FULL(sb), pb, err, 4);
+            mbar_wait(B_FULL(sb), pb, err, 4, wprof);
             tc_fence_after();
             if (elect_one_sync()) {
-              uint32_t b_lo = b_lo_base + sb * b_stage16;
+              const uint32_t b_lo = b_lo_base + sb * b_stage16;
               const int e_end = min(tg, nent - ent);
-              for (int e = 0; e < e_end; ++e, b_lo += b_ent16) {
-                const uint32_t a_lo = a_stage_lo + (uint32_t)t.ent_off[ent + e];
-                if (nterms == 1) {
-                  for (int j = 0; j < k16; ++j) {
-                    const uint64_t bdesc = ((uint64_t)desc_hi << 32) | (b_lo + (uint32_t)j * b_kstep16);
-                    const uint32_t a_j = a_lo + (uint32_t)j * a_kstep16;
-                    for (int mb = 0; mb < MB; ++mb)
-                      umma_f16(tmem_acc + (uint32_t)(mb * NPAD), ((uint64_t)desc_hi << 32) | (a_j + (uint32_t)mb * 128u), bdesc, idesc, acc_on);
-                    acc_on = 1u;
-                  }
+              const IssueArgs ia = {tmem_acc, a_stage_lo, b_lo, b_ent16, a_kstep16, b_kstep16, a_term16, b_term16, (uint32_t)NPAD, idesc,
+                                    ent_tab + ent, e_end, acc_on};
+              if (nterms == 1) {
+                if (k16 == 2) {
+                  if (MB == 2) issue_group<2, 2>(ia); else if (MB == 4) issue_group<2, 4>(ia); else if (MB == 8) issue_group<2, 8>(ia);
+                  else if (MB == 1) issue_group<2, 1>(ia); else issue_group_generic(ia, k16, MB, 1);
                 } else {
-                  for (int j = 0; j < k16; ++j) {
-                    for (int term = 0; term < 3; ++term) {                      // hi*hi, lo*hi, hi*lo
-                      const uint64_t bdesc = ((uint64_t)desc_hi << 32) | (b_lo + (uint32_t)j * b_kstep16 + (term == 2 ? b_term16 : 0u));
-                      const uint32_t a_j = a_lo + (uint32_t)j * a_kstep16 + (term == 1 ? a_term16 : 0u);
-                      for (int mb = 0; mb < MB; ++mb)
-                        umma_f16(tmem_acc + (uint32_t)(mb * NPAD), ((uint64_t)desc_hi << 32) | (a_j + (uint32_t)mb * 128u), bdesc, idesc, acc_on);
-                      acc_on = 1u;
-                    }
-                  }
+                  if (MB == 2) issue_group<1, 2>(ia); else if (MB == 4) issue_group<1, 4>(ia); else if (MB == 8) issue_group<1, 8>(ia);
+                  else if (MB == 1) issue_group<1, 1>(ia); else issue_group_generic(ia, k16, MB, 1);
                 }
+              } else {
+                issue_group_generic(ia, k16, MB, nterms);
               }
               umma_commit(B_EMPTY(sb));
             }
@@ -350,6 +590,7 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
         if (elect_one_sync()) umma_commit(ACC_FULL(buf));
         __syncwarp();
       }
+      wprof.flush(1, lane == 0);
     }
   } else if (warp < TC_FIRST_PROD_WARP) {
     // =========================== epilogue ===========================
@@ -376,11 +617,12 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
       }
     };
     uint32_t it = 0;
+    WaitProf wprof; wprof.init(args.prof);
     for (int tile = first_tile; tile < t.num_tiles; tile += tile_step, ++it) {
       const TileCoord tc = decode_tile(t, tile);
       if (tc.n != cur_n) { flush(); cur_n = tc.n; }
       const uint32_t buf = it & 1u;
-      mbar_wait(ACC_FULL(buf), (it >> 1) & 1u, err, 5);
+      mbar_wait(ACC_FULL(buf), (it >> 1) & 1u, err, 5, wprof);
       tc_fence_after();
       for (int mb = 0; mb < t.MB; ++mb) {
         const int m = mb * 128 + quad * 32 + lane;
@@ -390,18 +632,29 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
         const bool valid = ty < t.TH && tx < t.TW && oy < p.Ho && ox < p.Wo;
         const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + buf * (uint32_t)(t.MB * t.NPAD) + (uint32_t)(mb * t.NPAD);
         if (p.out_fmt == OUT_F32_NHWC_STATS) {
-          float* orow = (float*)p.out + (((size_t)tc.n * p.Ho + oy) * p.Wo + ox) * p.Cout;
+          const size_t orow_idx = (((size_t)tc.n * p.Ho + oy) * p.Wo + ox) * p.Cout;
+          float* orow = (float*)p.out + orow_idx;
+          __half* orow16 = (__half*)p.out + orow_idx;
 #pragma unroll
           for (int jc = 0; jc < 12; ++jc) {
             if (jc < njc) {
               float v[16];
               tmem_ld16(taddr + (uint32_t)(jc * 16), v);
               if (valid) {
-                float4* o4 = reinterpret_cast<float4*>(orow + jc * 16);
-                o4[0] = make_float4(v[0], v[1], v[2], v[3]);
-                o4[1] = make_float4(v[4], v[5], v[6], v[7]);
-                o4[2] = make_float4(v[8], v[9], v[10], v[11]);
-                o4[3] = make_float4(v[12], v[13], v[14], v[15]);
+                if (p.act16) {
+                  uint32_t h[8];
+#pragma unroll
+                  for (int i = 0; i < 8; ++i) h[i] = pack2(v[2 * i], v[2 * i + 1], 0);
+                  uint4* o4 = reinterpret_cast<uint4*>(orow16 + jc * 16);
+                  o4[0] = make_uint4(h[0], h[1], h[2], h[3]);
+                  o4[1] = make_uint4(h[4], h[5], h[6], h[7]);
+                } else {
+                  float4* o4 = reinterpret_cast<float4*>(orow + jc * 16);
+                  o4[0] = make_float4(v[0], v[1], v[2], v[3]);
+                  o4[1] = make_float4(v[4], v[5], v[6], v[7]);
+                  o4[2] = make_float4(v[8], v[9], v[10], v[11]);
+                  o4[3] = make_float4(v[12], v[13], v[14], v[15]);
+                }
               }
               // per-channel sum / sum of squares over the 32 rows of this warp: butterfly that halves
               // the number of live channels per step (16 -> 8 -> 4 -> 2 -> 1), then one pair add.
@@ -435,6 +688,7 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
       mbar_arrive(ACC_EMPTY(buf));
     }
     flush();
+    wprof.flush(2, warp == TC_FIRST_EPI_WARP && lane == 0);
   } else {
     // =========================== operand producers ===========================
     const int ptid = threadIdx.x - TC_FIRST_PROD_WARP * 32;
@@ -452,6 +706,10 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
     constexpr int U = 4;                    // items in flight per thread
     uint32_t sa = 0, pa = 0;
     int cur_n = -1;
+    if (nhwc && p.act16) {
+      if (has_resid) produce_act16<true>(p, t, smem_a, srcpix, coeff, A_FULL(0), A_EMPTY(0), err, args.prof, first_tile, tile_step, ptid);
+      else produce_act16<false>(p, t, smem_a, srcpix, coeff, A_FULL(0), A_EMPTY(0), err, args.prof, first_tile, tile_step, ptid);
+    } else
     for (int tile = first_tile; tile < t.num_tiles; tile += tile_step) {
       const TileCoord tc = decode_tile(t, tile);
       named_bar_sync(1, TC_PROD_THREADS);          // every producer is done with the previous tile's tables
@@ -495,7 +753,7 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
                 const float4* s4 = reinterpret_cast<const float4*>(srcf + off);
                 a[u][0] = __ldg(s4); a[u][1] = __ldg(s4 + 1);
                 if (has_resid) {
-                  const float4* r4 = reinterpret_cast<const float4*>(p.resid + off);
+                  const float4* r4 = reinterpret_cast<const float4*>((const float*)p.resid + off);
                   r[u][0] = __ldg(r4); r[u][1] = __ldg(r4 + 1);
                 }
               }
@@ -512,7 +770,7 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
                 x[u][i] = live ? v : 0.f;
               }
               if (live && (ent[u] & SIDE_BIT)) {
-                float4* d4 = reinterpret_cast<float4*>(p.side_out + (size_t)(ent[u] & (SIDE_BIT - 1)) * p.Cin + c0);
+                float4* d4 = reinterpret_cast<float4*>((float*)p.side_out + (size_t)(ent[u] & (SIDE_BIT - 1)) * p.Cin + c0);
                 d4[0] = make_float4(x[u][0], x[u][1], x[u][2], x[u][3]);
                 d4[1] = make_float4(x[u][4], x[u][5], x[u][6], x[u][7]);
               }

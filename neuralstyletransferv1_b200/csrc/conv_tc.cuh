@@ -48,6 +48,7 @@ struct TcArgs {
   TcPlan t;
   const void* wpack;        // [chunk][group][term][entry in group][plane][NPAD][8] 16-bit
   unsigned int* err_flag;   // set non-zero when a pipeline wait times out
+  unsigned long long* prof; // debug (NST_TC_PROF=1): [code 1..6] cycles waited per barrier kind, [8+role] role cycles; or null
 };
 
 cudaError_t launch_conv_tc(const TcArgs& a, int num_sms, cudaStream_t stream);

@@ -198,7 +198,8 @@ struct nst_handle {
   int out_H = 0, out_W = 0;
   std::vector<LayerPlan> plans;
   BufDims bufs[NBUF];
-  size_t act_floats_per_frame = 0;
+  size_t act_floats_per_frame = 0;   // activation ELEMENTS per frame (fp16 or fp32, see act16)
+  int act16 = 0;
   size_t stats_doubles_per_frame = 0;
   size_t workspace_bytes = 0;
   unsigned int* err_host = nullptr;
@@ -206,6 +207,7 @@ struct nst_handle {
   long long launches = 0;
   int microbatch = 8;
   int dbg = 0;
+  unsigned long long* prof_dev = nullptr;     // NST_TC_PROF=1: per-role wait-cycle counters (debug)
   unsigned long long tc_layer_mask = ~0ull;   // debug: bit i clear -> layer i runs on the direct kernel
 };
 
@@ -245,14 +247,15 @@ static void tc_plan_static(const LayerSpec& s, int precision, TcPlan& t) {
   if (precision == NST_PREC_F16X3) { t.nterms = 3; t.a_tplanes = 2; t.b_tplanes = 2; }
   else { t.nterms = 1; t.a_tplanes = 1; t.b_tplanes = 1; }
   t.b_ent_bytes = (uint32_t)((t.pair_mode ? 2 : t.planes) * t.NPAD * 16);
-  int tg = (int)(8192 / (t.b_ent_bytes * t.b_tplanes));
+  // weight stage: up to 24 KB (3 taps of a 128->128 layer) so one mbarrier wait feeds >= 12 MMAs
+  int tg = (int)(24576 / (t.b_ent_bytes * t.b_tplanes));
   tg = std::max(1, std::min(tg, t.nent));
   if (s.ks == 9 && !t.pair_mode) tg = std::min(tg, 9);
   t.tg = tg;
   t.ngroups = ceil_div(t.nent, tg);
   t.b_term_bytes = (uint32_t)tg * t.b_ent_bytes;
   t.b_stage_bytes = t.b_term_bytes * (uint32_t)t.b_tplanes;
-  t.b_stages = t.b_stage_bytes <= 8192 ? 6 : (t.b_stage_bytes <= 16384 ? 4 : 2);
+  t.b_stages = t.b_stage_bytes <= 8192 ? 6 : (t.b_stage_bytes <= 16384 ? 4 : 3);
   int mb = 256 / t.NPAD;                  // two accumulator buffers of MB*NPAD columns in 512
   t.MB = std::max(1, std::min(mb, 8));
 }
@@ -311,8 +314,8 @@ static bool tc_plan_geometry(const ConvParams& p, TcPlan& t) {
     t.a_term_bytes = t.a_plane_bytes * (uint32_t)t.planes;
     t.a_stage_bytes = (uint32_t)round_up((size_t)t.a_term_bytes * t.a_tplanes, 128);
     const int b_total = t.b_stages * (int)t.b_stage_bytes;
-    // barriers + TMEM slot + per-tile source table [NPOS] + per-sample norm coefficients [Cin<=256]
-    const int bar_bytes = 256 + (int)round_up((size_t)t.NPOS * 4, 16) + 256 * 8;
+    // barriers + TMEM slot + two per-tile source tables [NPOS] (current / next tile) + per-sample norm coefficients [Cin<=256]
+    const int bar_bytes = 640 + 2 * (int)round_up((size_t)t.NPOS * 4, 16) + 256 * 8;
     const int avail = TC_SMEM_LIMIT - b_total - bar_bytes;
     int a_stages = avail / (int)t.a_stage_bytes;
     const int want = t.nchunks == 1 ? 2 : 3;
@@ -397,6 +400,8 @@ extern "C" int nst_create(int device, int arch, int precision, nst_handle** out)
   CUDA_TRY(cudaSetDevice(device));
   nst_handle* h = new nst_handle();
   h->device = device; h->arch = arch; h->precision = precision;
+  h->act16 = precision == NST_PREC_F16 ? 1 : 0;
+  if (const char* a = getenv("NST_ACT16")) h->act16 = atoi(a) != 0 && precision != NST_PREC_F16X3;
   h->num_sms = prop.multiProcessorCount;
   h->specs = arch == NST_ARCH_JOHNSON ? johnson_layers() : (arch == NST_ARCH_NST ? nst_layers() : reconet_layers());
   h->dev.resize(h->specs.size());
@@ -408,6 +413,7 @@ extern "C" int nst_create(int device, int arch, int precision, nst_handle** out)
   *h->err_host = 0;
   e = cudaHostGetDevicePointer((void**)&h->err_dev, h->err_host, 0);
   if (e == cudaSuccess) e = conv_tc_init();
+  if (e == cudaSuccess && getenv("NST_TC_PROF") && atoi(getenv("NST_TC_PROF"))) e = cudaMalloc((void**)&h->prof_dev, 16 * sizeof(unsigned long long));
   if (e != cudaSuccess) { cudaFreeHost(h->err_host); delete h; return fail(NST_ERR_CUDA, "nst_create: %s", cudaGetErrorString(e)); }
   *out = h;
   return NST_OK;
@@ -423,6 +429,7 @@ extern "C" void nst_destroy(nst_handle* h) {
   cudaSetDevice(h->device);
   for (auto& d : h->dev) free_layer(d);
   if (h->err_host) cudaFreeHost(h->err_host);
+  cudaFree(h->prof_dev);
   delete h;
 }
 
@@ -544,6 +551,7 @@ static int make_plan(nst_handle* h, int N, int H, int W) {
     p.pad_t = p.pad_l = s.pad;
     p.pre_relu = s.pre_relu; p.post_relu = s.post_relu; p.tanh_out = s.tanh_out;
     p.blend = 1.f;
+    p.act16 = h->act16;
     if (s.src == BUF_IMAGE) { p.Hs = H; p.Ws = W; }
     else {
       const BufDims& bd = h->bufs[s.src];
@@ -584,8 +592,12 @@ static int make_plan(nst_handle* h, int N, int H, int W) {
       bd.elems = std::max(bd.elems, (size_t)s.cin * p.Hs * p.Ws);
     }
     lp.flops = 2.0 * p.Ho * p.Wo * (double)s.cout * s.cin * s.ks * s.ks;      // per frame
-    lp.bytes = 4.0 * ((double)p.Hs * p.Ws * s.cin * (s.resid >= 0 ? 2 : 1) + (double)p.Ho * p.Wo * s.cout +
-                      (s.side >= 0 ? (double)p.Hs * p.Ws * s.cin : 0.0));
+    {   // algorithmic HBM bytes per frame: each operand once, image tensors at their own element size
+      const double esz = h->act16 ? 2.0 : 4.0;
+      const double in_b = s.src == BUF_IMAGE ? 3.0 * p.Hs * p.Ws : esz * p.Hs * p.Ws * s.cin;
+      const double out_b = s.out == BUF_IMAGE ? 3.0 * p.Ho * p.Wo : esz * p.Ho * p.Wo * s.cout;
+      lp.bytes = in_b + out_b + esz * (double)p.Hs * p.Ws * s.cin * ((s.resid >= 0 ? 1 : 0) + (s.side >= 0 ? 1 : 0));
+    }
     lp.use_tc = h->dev[li].tc_ok && ((h->tc_layer_mask >> li) & 1ull);
     if (lp.use_tc) {
       lp.t = h->dev[li].tc_static;
@@ -599,7 +611,7 @@ static int make_plan(nst_handle* h, int N, int H, int W) {
   }
   h->act_floats_per_frame = off;
   h->stats_doubles_per_frame = stats_off;
-  h->workspace_bytes = round_up(off * sizeof(float) * nb, 256) + round_up(stats_off * sizeof(double) * nb, 256) + 256;
+  h->workspace_bytes = round_up(off * (h->act16 ? 2 : 4) * nb, 256) + round_up(stats_off * sizeof(double) * nb, 256) + 256;
   h->plan_N = N; h->plan_H = H; h->plan_W = W; h->plan_nb = nb;
   return NST_OK;
 }
@@ -636,8 +648,9 @@ static int run_forward(nst_handle* h, const IoSpec& io, int N, int H, int W, voi
   if (((uintptr_t)workspace & 255) != 0) return fail(NST_ERR_INVALID, "forward: workspace must be 256-byte aligned");
   if (*h->err_host != 0) return fail(NST_ERR_CUDA, "forward: a previous kernel reported pipeline error 0x%08x", *h->err_host);
   const int nb = h->plan_nb;
-  float* act = (float*)workspace;
-  double* stats = (double*)((char*)workspace + round_up(h->act_floats_per_frame * sizeof(float) * nb, 256));
+  const size_t esz = h->act16 ? 2 : 4;
+  char* act = (char*)workspace;
+  double* stats = (double*)((char*)workspace + round_up(h->act_floats_per_frame * esz * nb, 256));
   const size_t stats_bytes = h->stats_doubles_per_frame * sizeof(double) * nb;
   const int Ho = h->out_H, Wo = h->out_W;
   const size_t in_px = (size_t)H * W * 3, out_px = (size_t)Ho * Wo * 3;
@@ -658,7 +671,7 @@ static int run_forward(nst_handle* h, const IoSpec& io, int N, int H, int W, voi
       LayerPlan& lp = h->plans[li];
       ConvParams p = lp.p;
       p.N = n;
-      auto buf = [&](int b) -> float* { return act + h->bufs[b].off * nb; };
+      auto buf = [&](int b) -> void* { return act + h->bufs[b].off * nb * esz; };
       if (s.src == BUF_IMAGE) {
         p.in_fmt = io.in_fmt;
         p.src = (const char*)io.x + (size_t)n0 * in_px * in_elt;
@@ -692,7 +705,19 @@ static int run_forward(nst_handle* h, const IoSpec& io, int N, int H, int W, voi
         a.p = p; a.t = lp.t;
         a.t.num_tiles = lp.t.tiles_x * lp.t.tiles_y * n;
         a.wpack = d.wpack; a.err_flag = h->err_dev;
+        a.prof = layer_ms ? h->prof_dev : nullptr;
+        if (a.prof) CUDA_TRY(cudaMemsetAsync(a.prof, 0, 16 * sizeof(unsigned long long), stream));
         CUDA_TRY(launch_conv_tc(a, h->num_sms, stream));
+        if (a.prof) {
+          unsigned long long pc[16];
+          CUDA_TRY(cudaMemcpyAsync(pc, a.prof, sizeof(pc), cudaMemcpyDeviceToHost, stream));
+          CUDA_TRY(cudaStreamSynchronize(stream));
+          const double g = std::min(a.t.num_tiles, h->num_sms);
+          fprintf(stderr, "[tcprof] %-12s tiles=%d ctas=%.0f | per-CTA kcycles: loader total %.0f wait B_EMPTY %.0f | mma total %.0f wait ACC_EMPTY %.0f A_FULL %.0f B_FULL %.0f | "
+                          "epi total %.0f wait ACC_FULL %.0f | prod total %.0f wait A_EMPTY %.0f\n", s.name.c_str(), a.t.num_tiles, g,
+                  pc[8] / g / 1e3, pc[1] / g / 1e3, pc[9] / g / 1e3, pc[2] / g / 1e3, pc[3] / g / 1e3, pc[4] / g / 1e3, pc[10] / g / 1e3, pc[5] / g / 1e3,
+                  pc[11] / g / 1e3, pc[6] / g / 1e3);
+        }
       } else {
         CUDA_TRY(launch_conv_direct(p, d.wdir, stream));
       }
@@ -817,6 +842,7 @@ extern "C" int nst_describe_plan(int arch, int precision, int N, int H, int W, c
   if (arch < 0 || arch > 2 || precision < 0 || precision > 3) return fail(NST_ERR_INVALID, "nst_describe_plan: bad arch/precision");
   nst_handle h;
   h.arch = arch; h.precision = precision;
+  h.act16 = precision == NST_PREC_F16 ? 1 : 0;
   h.specs = arch == NST_ARCH_JOHNSON ? johnson_layers() : (arch == NST_ARCH_NST ? nst_layers() : reconet_layers());
   h.dev.resize(h.specs.size());
   if (const char* mbs = getenv("NST_MICROBATCH")) h.microbatch = std::max(1, atoi(mbs));

@@ -14,6 +14,9 @@
 
 namespace nst {
 
+// IN_F32_NHWC / OUT_F32_NHWC_STATS name the intermediate-activation formats; their element type is
+// fp32, or fp16 when ConvParams::act16 is set (the default NST_PREC_F16 mode stores raw conv outputs
+// as fp16: half the HBM traffic, parity cost ~2 dB PSNR -- oracle/precision_study.py STORAGE=1).
 enum InFmt { IN_F32_NHWC = 0, IN_F32_NCHW3 = 1, IN_U8_NHWC3 = 2 };
 enum OutFmt { OUT_F32_NHWC_STATS = 0, OUT_F32_NCHW3 = 1, OUT_U8_NHWC3 = 2 };
 enum MapMode { MAP_IDENTITY = 0, MAP_UP2 = 1, MAP_ZERO_INSERT2 = 2, MAP_PREPAD_REFLECT = 3 };
@@ -23,9 +26,10 @@ constexpr float kInEps = 1e-5f;   // torch.nn.InstanceNorm2d default eps
 
 struct ConvParams {
   // ---- source ----
-  const void* src;          // IN_F32_NHWC: float [N,Hs,Ws,Cin]; IN_F32_NCHW3: float [N,3,Hs,Ws]; IN_U8_NHWC3: u8 [N,Hs,Ws,3]
-  const float* resid;       // float NHWC [N,Hs,Ws,Cin] added after norm(+relu), or null
-  float* side_out;          // float NHWC [N,Hs,Ws,Cin]: the transformed input is stored here (or null)
+  const void* src;          // IN_F32_NHWC: act [N,Hs,Ws,Cin]; IN_F32_NCHW3: float [N,3,Hs,Ws]; IN_U8_NHWC3: u8 [N,Hs,Ws,3]
+  const void* resid;        // act NHWC [N,Hs,Ws,Cin] added after norm(+relu), or null
+  void* side_out;           // act NHWC [N,Hs,Ws,Cin]: the transformed input is stored here (or null)
+  int act16;                // element type of the "act" tensors (src, resid, side_out, out): 1 = fp16, 0 = fp32
   const double* in_stats;   // [N][Cin][2] (sum, sumsq) of src, or null (no norm)
   const float* in_gamma;    // [Cin]
   const float* in_beta;     // [Cin]
@@ -53,6 +57,13 @@ struct ConvParams {
   float blend;              // uniform blend in [0,1); >= 1 disables
   int composite_mode;
 };
+
+__device__ __forceinline__ float ld_act(const void* p, size_t i, int act16) {
+  return act16 ? __half2float(((const __half*)p)[i]) : ((const float*)p)[i];
+}
+__device__ __forceinline__ void st_act(void* p, size_t i, float v, int act16) {
+  if (act16) ((__half*)p)[i] = __float2half_rn(v); else ((float*)p)[i] = v;
+}
 
 // Map one conv-space coordinate u (already minus the conv padding) to a source coordinate.
 // Returns -1 when the tap reads a structural zero (zero padding / zero insertion).
