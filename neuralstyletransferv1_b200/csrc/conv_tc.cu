@@ -322,7 +322,7 @@ __device__ __forceinline__ void prod_load(ProdBatch<HAS_RESID>& B, const ProdCur
 #pragma unroll
   for (int u = 0; u < PU; ++u) {
     const int idx = ptid + (c.b * PU + u) * TC_PROD_THREADS;
-    B.ent[u] = (valid && idx < nitems) ? tbl[idx >> pshift] : -2;
+    B.ent[u] = (valid && idx < nitems && !(t.dbg & 2)) ? tbl[idx >> pshift] : -2;
   }
 #pragma unroll
   for (int u = 0; u < PU; ++u) {
@@ -462,6 +462,76 @@ __device__ void produce_act16(const ConvParams& p, const TcPlan& t, uint8_t* sme
 // ---------------------------------------------------------------------------------------------
 // the kernel
 // ---------------------------------------------------------------------------------------------
+
+// ---------------------------------------------------------------------------------------------
+// MMA issuer role.  The whole warp walks the pipeline converged and one elected lane issues (the
+// CUTLASS idiom): ptxas then keeps every descriptor in uniform registers.  The role is a template
+// on (K16, MB) dispatched ONCE per kernel: measured with the other roles switched off, the same
+// loop with a per-weight-stage runtime dispatch (jump table + descriptor set-up from constant
+// memory) cost ~106 cycles per N=128 MMA against 70 for tools/umma_pattern.cu -- the tensor pipe's
+// issue queue is short, so every bubble at a stage boundary is exposed.
+// ---------------------------------------------------------------------------------------------
+struct MmaCtx {
+  uint32_t smem_a, smem_b, bar0, tmem_base;
+  const uint32_t* ent_tab;
+  unsigned int* err;
+  unsigned long long* prof;
+  int first_tile, tile_step;
+};
+
+template <int K16, int MB_>
+__device__ __noinline__ void mma_role(const TcPlan& t, const MmaCtx c) {
+  const uint32_t idesc = make_idesc(t.NPAD, t.is_bf16);
+  const uint32_t a_lbo16 = (t.pair_mode ? 16u : t.a_plane_bytes) >> 4;
+  const uint32_t a_lo_base = ((c.smem_a >> 4) & 0x3FFFu) | (a_lbo16 << 16);
+  const uint32_t b_lo_base = ((c.smem_b >> 4) & 0x3FFFu) | ((uint32_t)t.NPAD << 16);   // LBO = NPAD*16 B
+  const uint32_t a_kstep16 = (2u * t.a_plane_bytes) >> 4;
+  const uint32_t b_kstep16 = 2u * (uint32_t)t.NPAD;
+  const uint32_t a_stage16 = t.a_stage_bytes >> 4, b_stage16 = t.b_stage_bytes >> 4;
+  const uint32_t a_term16 = t.a_term_bytes >> 4, b_term16 = t.b_term_bytes >> 4, b_ent16 = t.b_ent_bytes >> 4;
+  const int MB = MB_ ? MB_ : t.MB, NPAD = t.NPAD, k16 = t.k16_per_ent, nterms = t.nterms, tg = t.tg, nent = t.nent;
+  const int nchunks = t.nchunks, ngroups = t.ngroups, num_tiles = t.num_tiles, dbg = t.dbg;
+  const uint32_t a_stages = (uint32_t)t.a_stages, b_stages = (uint32_t)t.b_stages;
+  const uint32_t A_FULL0 = c.bar0, A_EMPTY0 = c.bar0 + 8u * TC_MAX_A_STAGES, B_FULL0 = c.bar0 + 8u * (2 * TC_MAX_A_STAGES),
+                 B_EMPTY0 = B_FULL0 + 8u * TC_MAX_B_STAGES, ACC_FULL0 = B_FULL0 + 8u * (2 * TC_MAX_B_STAGES), ACC_EMPTY0 = ACC_FULL0 + 16u;
+  WaitProf wprof; wprof.init(c.prof);
+  uint32_t sa = 0, pa = 0, sb = 0, pb = 0, it = 0;
+  for (int tile = c.first_tile; tile < num_tiles; tile += c.tile_step, ++it) {
+    const uint32_t buf = it & 1u;
+    if (!(dbg & 32)) mbar_wait(ACC_EMPTY0 + 8u * buf, ((it >> 1) & 1u) ^ 1u, c.err, 2, wprof);
+    tc_fence_after();
+    const uint32_t tmem_acc = c.tmem_base + buf * (uint32_t)(MB * NPAD);
+    uint32_t acc_on = 0u;
+    for (int ch = 0; ch < nchunks; ++ch) {
+      if (!(dbg & 16)) mbar_wait(A_FULL0 + 8u * sa, pa, c.err, 3, wprof);
+      tc_fence_after();
+      const uint32_t a_stage_lo = a_lo_base + sa * a_stage16;
+      int ent = 0;
+      for (int g = 0; g < ngroups; ++g) {
+        if (!(dbg & 64)) mbar_wait(B_FULL0 + 8u * sb, pb, c.err, 4, wprof);
+        tc_fence_after();
+        if (elect_one_sync()) {
+          const IssueArgs ia = {tmem_acc, a_stage_lo, b_lo_base + sb * b_stage16, b_ent16, a_kstep16, b_kstep16, a_term16, b_term16, (uint32_t)NPAD, idesc,
+                                c.ent_tab + ent, min(tg, nent - ent), acc_on};
+          if (K16 != 0) issue_group<(K16 ? K16 : 1), (MB_ ? MB_ : 1)>(ia);
+          else issue_group_generic(ia, k16, MB, nterms);
+          umma_commit(B_EMPTY0 + 8u * sb);
+        }
+        __syncwarp();
+        acc_on = 1u;
+        ent += tg;
+        if (++sb == b_stages) { sb = 0; pb ^= 1u; }
+      }
+      if (elect_one_sync()) umma_commit(A_EMPTY0 + 8u * sa);
+      __syncwarp();
+      if (++sa == a_stages) { sa = 0; pa ^= 1u; }
+    }
+    if (elect_one_sync()) umma_commit(ACC_FULL0 + 8u * buf);
+    __syncwarp();
+  }
+  wprof.flush(1, (threadIdx.x & 31) == 0);
+}
+
 constexpr int NBARS = 2 * TC_MAX_A_STAGES + 2 * TC_MAX_B_STAGES + 4;
 
 __global__ void __launch_bounds__(TC_THREADS, 1)
@@ -507,7 +577,7 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
 
   if (warp == 0) {
     // =========================== weight loader ===========================
-    if (lane == 0) {
+    if (lane == 0 && !(t.dbg & 64)) {
       WaitProf wprof; wprof.init(args.prof);
       uint32_t sb = 0, pb = 0;
       const uint8_t* wp = reinterpret_cast<const uint8_t*>(args.wpack);
@@ -515,6 +585,7 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
       for (int tile = first_tile; tile < t.num_tiles; tile += tile_step) {
         for (int g = 0; g < nstage_per_tile; ++g) {
           mbar_wait(B_EMPTY(sb), pb ^ 1u, err, 1, wprof);
+          if (t.dbg & 8) { mbar_arrive(B_FULL(sb)); if (++sb == (uint32_t)t.b_stages) { sb = 0; pb ^= 1u; } continue; }
           mbar_arrive_expect_tx(B_FULL(sb), t.b_stage_bytes);
           bulk_g2s(smem_u32(smem_b + (size_t)sb * t.b_stage_bytes), wp + (size_t)g * t.b_stage_bytes,
                    t.b_stage_bytes, B_FULL(sb));
@@ -525,73 +596,16 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
     }
   } else if (warp == 1) {
     // =========================== MMA issuer ===========================
-    // The whole warp walks the pipeline converged and one elected lane issues (the CUTLASS idiom):
-    // ptxas then keeps every descriptor in uniform registers.  Measured with tools/umma_bench.cu: a
-    // tcgen05.mma runs at its floor (64 cycles for M=128,N=128,K=16) only when the issuing loop costs
-    // less than that; building 64-bit descriptors from scratch per MMA in divergent code cost 170-370
-    // cycles per MMA.  So: descriptor high words are constants, low words are (addr>>4)|(LBO>>4)<<16
-    // and every step below is one 32-bit add in 16-byte units.
-    {
-      const uint32_t idesc = make_idesc(t.NPAD, t.is_bf16);
-      const uint32_t a_lbo16 = (t.pair_mode ? 16u : t.a_plane_bytes) >> 4;
-      const uint32_t a_lo_base = ((smem_u32(smem_a) >> 4) & 0x3FFFu) | (a_lbo16 << 16);
-      const uint32_t b_lo_base = ((smem_u32(smem_b) >> 4) & 0x3FFFu) | ((uint32_t)t.NPAD << 16);   // LBO = NPAD*16 B
-      const uint32_t a_kstep16 = (2u * t.a_plane_bytes) >> 4;
-      const uint32_t b_kstep16 = 2u * (uint32_t)t.NPAD;
-      const uint32_t a_stage16 = t.a_stage_bytes >> 4, b_stage16 = t.b_stage_bytes >> 4;
-      const uint32_t a_term16 = t.a_term_bytes >> 4, b_term16 = t.b_term_bytes >> 4, b_ent16 = t.b_ent_bytes >> 4;
-      const int MB = t.MB, NPAD = t.NPAD, k16 = t.k16_per_ent, nterms = t.nterms, tg = t.tg, nent = t.nent;
-      WaitProf wprof; wprof.init(args.prof);
-      // tap -> A position offset table in shared memory (a uniform LDS per tap instead of an indexed constant load)
-      for (int i = lane; i < t.nent; i += 32) ent_tab[i] = (uint32_t)t.ent_off[i];
-      __syncwarp();
-      uint32_t sa = 0, pa = 0, sb = 0, pb = 0, it = 0;
-      for (int tile = first_tile; tile < t.num_tiles; tile += tile_step, ++it) {
-        const uint32_t buf = it & 1u;
-        mbar_wait(ACC_EMPTY(buf), ((it >> 1) & 1u) ^ 1u, err, 2, wprof);
-        tc_fence_after();
-        const uint32_t tmem_acc = tmem_base + buf * (uint32_t)(MB * NPAD);
-        uint32_t acc_on = 0u;
-        for (int ch = 0; ch < t.nchunks; ++ch) {
-          mbar_wait(A_FULL(sa), pa, err, 3, wprof);
-          tc_fence_after();
-          const uint32_t a_stage_lo = a_lo_base + sa * a_stage16;
-          int ent = 0;
-          for (int g = 0; g < t.ngroups; ++g) {
-            mbar_wait(B_FULL(sb), pb, err, 4, wprof);
-            tc_fence_after();
-            if (elect_one_sync()) {
-              const uint32_t b_lo = b_lo_base + sb * b_stage16;
-              const int e_end = min(tg, nent - ent);
-              const IssueArgs ia = {tmem_acc, a_stage_lo, b_lo, b_ent16, a_kstep16, b_kstep16, a_term16, b_term16, (uint32_t)NPAD, idesc,
-                                    ent_tab + ent, e_end, acc_on};
-              if (nterms == 1) {
-                if (k16 == 2) {
-                  if (MB == 2) issue_group<2, 2>(ia); else if (MB == 4) issue_group<2, 4>(ia); else if (MB == 8) issue_group<2, 8>(ia);
-                  else if (MB == 1) issue_group<2, 1>(ia); else issue_group_generic(ia, k16, MB, 1);
-                } else {
-                  if (MB == 2) issue_group<1, 2>(ia); else if (MB == 4) issue_group<1, 4>(ia); else if (MB == 8) issue_group<1, 8>(ia);
-                  else if (MB == 1) issue_group<1, 1>(ia); else issue_group_generic(ia, k16, MB, 1);
-                }
-              } else {
-                issue_group_generic(ia, k16, MB, nterms);
-              }
-              umma_commit(B_EMPTY(sb));
-            }
-            __syncwarp();
-            acc_on = 1u;
-            ent += tg;
-            if (++sb == (uint32_t)t.b_stages) { sb = 0; pb ^= 1u; }
-          }
-          if (elect_one_sync()) umma_commit(A_EMPTY(sa));
-          __syncwarp();
-          if (++sa == (uint32_t)t.a_stages) { sa = 0; pa ^= 1u; }
-        }
-        if (elect_one_sync()) umma_commit(ACC_FULL(buf));
-        __syncwarp();
-      }
-      wprof.flush(1, lane == 0);
-    }
+    for (int i = lane; i < t.nent; i += 32) ent_tab[i] = (uint32_t)t.ent_off[i];
+    __syncwarp();
+    const MmaCtx mc = {smem_u32(smem_a), smem_u32(smem_b), bar0, tmem_base, ent_tab, err, args.prof, first_tile, tile_step};
+    if (t.nterms == 1 && t.k16_per_ent == 2 && t.MB == 2) mma_role<2, 2>(t, mc);
+    else if (t.nterms == 1 && t.k16_per_ent == 2 && t.MB == 4) mma_role<2, 4>(t, mc);
+    else if (t.nterms == 1 && t.k16_per_ent == 2 && t.MB == 8) mma_role<2, 8>(t, mc);
+    else if (t.nterms == 1 && t.k16_per_ent == 2 && t.MB == 1) mma_role<2, 1>(t, mc);
+    else if (t.nterms == 1 && t.k16_per_ent == 1 && t.MB == 8) mma_role<1, 8>(t, mc);
+    else if (t.nterms == 1 && t.k16_per_ent == 1 && t.MB == 4) mma_role<1, 4>(t, mc);
+    else mma_role<0, 0>(t, mc);
   } else if (warp < TC_FIRST_PROD_WARP) {
     // =========================== epilogue ===========================
     const int quad = warp & 3;                        // TMEM lane quadrant this warp may read
@@ -618,13 +632,13 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
     };
     uint32_t it = 0;
     WaitProf wprof; wprof.init(args.prof);
-    for (int tile = first_tile; tile < t.num_tiles; tile += tile_step, ++it) {
+    for (int tile = first_tile; tile < ((t.dbg & 32) ? 0 : t.num_tiles); tile += tile_step, ++it) {
       const TileCoord tc = decode_tile(t, tile);
       if (tc.n != cur_n) { flush(); cur_n = tc.n; }
       const uint32_t buf = it & 1u;
       mbar_wait(ACC_FULL(buf), (it >> 1) & 1u, err, 5, wprof);
       tc_fence_after();
-      for (int mb = 0; mb < t.MB; ++mb) {
+      for (int mb = 0; mb < ((t.dbg & 4) ? 0 : t.MB); ++mb) {
         const int m = mb * 128 + quad * 32 + lane;
         const int ty = m / t.P;
         const int tx = m - ty * t.P;
@@ -639,8 +653,9 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
           for (int jc = 0; jc < 12; ++jc) {
             if (jc < njc) {
               float v[16];
+              if (t.dbg & 512) { for (int i = 0; i < 16; ++i) v[i] = 0.f; } else
               tmem_ld16(taddr + (uint32_t)(jc * 16), v);
-              if (valid) {
+              if (valid && !(t.dbg & 128)) {
                 if (p.act16) {
                   uint32_t h[8];
 #pragma unroll
@@ -658,6 +673,7 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
               }
               // per-channel sum / sum of squares over the 32 rows of this warp: butterfly that halves
               // the number of live channels per step (16 -> 8 -> 4 -> 2 -> 1), then one pair add.
+              if (t.dbg & 256) continue;
               float s[16], q[16];
 #pragma unroll
               for (int i = 0; i < 16; ++i) { s[i] = valid ? v[i] : 0.f; q[i] = s[i] * s[i]; }
@@ -706,7 +722,8 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
     constexpr int U = 4;                    // items in flight per thread
     uint32_t sa = 0, pa = 0;
     int cur_n = -1;
-    if (nhwc && p.act16) {
+    if (t.dbg & 16) {
+    } else if (nhwc && p.act16) {
       if (has_resid) produce_act16<true>(p, t, smem_a, srcpix, coeff, A_FULL(0), A_EMPTY(0), err, args.prof, first_tile, tile_step, ptid);
       else produce_act16<false>(p, t, smem_a, srcpix, coeff, A_FULL(0), A_EMPTY(0), err, args.prof, first_tile, tile_step, ptid);
     } else
