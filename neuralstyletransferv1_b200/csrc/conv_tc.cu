@@ -548,6 +548,7 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
   uint32_t* ent_tab = tmem_slot + 4;                                         // [TC_MAX_ENT rounded to 84] tap offsets (MMA warp)
   int* srcpix = reinterpret_cast<int*>(ent_tab + 84);                       // [NPOS] source table of the current tile
   float2* coeff = reinterpret_cast<float2*>(srcpix + 2 * ((t.NPOS + 3) & ~3));  // [Cin] InstanceNorm (scale, shift) of sample n (two source tables before it)
+  float* fold_ring = reinterpret_cast<float*>(coeff + 256);                   // [256][TC_FOLD_PITCH] (fold_s layers only)
 
   const uint32_t bar0 = smem_u32(bars);
   auto A_FULL = [&](int s) { return bar0 + 8u * (uint32_t)s; };
@@ -632,6 +633,51 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
     };
     uint32_t it = 0;
     WaitProf wprof; wprof.init(args.prof);
+    if (t.fold_s) {
+      // Image layer with the horizontal taps folded into N:  TMEM holds T[m][s*3+co] = sum_{r,ci} in[m + r*P][ci] w[co][ci][r][s];
+      // out[m][co] = sum_s T[m + s][s*3 + co].  Rows are exchanged through a two-block ring in shared memory: block mb is
+      // written to half (mb & 1), then every thread finishes the output 8 rows behind its own TMEM row.
+      const int tid = quad * 32 + lane;             // TMEM lane (row of the M block) this thread reads
+      const float b0 = p.bias[0], b1 = p.bias[1], b2 = p.bias[2];
+      uint32_t it = 0;
+      WaitProf wprof; wprof.init(args.prof);
+      for (int tile = first_tile; tile < ((t.dbg & 32) ? 0 : t.num_tiles); tile += tile_step, ++it) {
+        const TileCoord tc = decode_tile(t, tile);
+        const uint32_t buf = it & 1u;
+        mbar_wait(ACC_FULL(buf), (it >> 1) & 1u, err, 5, wprof);
+        tc_fence_after();
+        for (int mb = 0; mb < t.MB; ++mb) {
+          const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + buf * (uint32_t)(t.MB * t.NPAD) + (uint32_t)(mb * t.NPAD);
+          float v0[16], v1[16];
+          tmem_ld16(taddr, v0);
+          tmem_ld16(taddr + 16u, v1);
+          if (mb == t.MB - 1) { tc_fence_before(); mbar_arrive(ACC_EMPTY(buf)); }
+          named_bar_sync(3, 128);                       // readers of the previous block are done with this half's neighbour rows
+          float* row = fold_ring + (size_t)((mb & 1) * 128 + tid) * TC_FOLD_PITCH;
+#pragma unroll
+          for (int i = 0; i < 16; ++i) row[i] = v0[i];
+#pragma unroll
+          for (int i = 0; i < 11; ++i) row[16 + i] = v1[i];
+          named_bar_sync(4, 128);
+          const int m = mb * 128 + tid - 8;
+          if (m >= 0) {
+            const int ty = m / t.P, tx = m - ty * t.P;
+            const int oy = tc.ty0 + ty, ox = tc.tx0 + tx;
+            if (ty < t.TH && tx < t.TW && oy < p.Ho && ox < p.Wo) {
+              float a0 = b0, a1 = b1, a2 = b2;
+#pragma unroll
+              for (int sx = 0; sx < 9; ++sx) {
+                const int mm = m + sx;
+                const float* rr = fold_ring + (size_t)(((mm >> 7) & 1) * 128 + (mm & 127)) * TC_FOLD_PITCH + sx * 3;
+                a0 += rr[0]; a1 += rr[1]; a2 += rr[2];
+              }
+              store_image(p, tc.n, oy, ox, a0, a1, a2);
+            }
+          }
+        }
+      }
+      wprof.flush(2, warp == TC_FIRST_EPI_WARP && lane == 0);
+    } else
     for (int tile = first_tile; tile < ((t.dbg & 32) ? 0 : t.num_tiles); tile += tile_step, ++it) {
       const TileCoord tc = decode_tile(t, tile);
       if (tc.n != cur_n) { flush(); cur_n = tc.n; }

@@ -13,6 +13,8 @@ constexpr int TC_THREADS = (TC_FIRST_PROD_WARP + TC_PROD_WARPS) * 32;   // 448
 constexpr int TC_MAX_A_STAGES = 4;
 constexpr int TC_MAX_B_STAGES = 8;
 constexpr int TC_SMEM_LIMIT = 227 * 1024;
+constexpr int TC_FOLD_PITCH = 29;      // floats per ring row (27 used; odd pitch = conflict-free)
+constexpr int TC_FOLD_RING_BYTES = 256 * TC_FOLD_PITCH * 4;
 
 // GEMM view of one layer:  D[m, co] = sum_{entry e, k} A[m + ent_off[e], k] * W[e][k][co]
 //   m      : flat position inside the CTA tile's halo buffer (pitch P), M = MB*128 rows
@@ -36,7 +38,9 @@ struct TcPlan {
   int nterms;               // 1, or 3 (hi*hi + lo*hi + hi*lo)
   int a_tplanes, b_tplanes; // operand planes kept (1, or 2 = hi and lo)
   int is_bf16;
-  int dbg;                  // debug bits: 1 = swap LBO/SBO roles in the UMMA descriptors
+  int fold_s;               // image layer (Cout = 3, k9): GEMM N = (horizontal tap s, co) = 27 of 32 columns, entries = the 9 filter
+                            // rows; the epilogue sums T[m + s][s*3 + co] over s through a shared-memory ring (9x fewer MMAs)
+  int dbg;                  // debug bits (tools/dbg_sweep.sh): switch pipeline roles off one at a time
   uint32_t a_plane_bytes, a_term_bytes, a_stage_bytes;
   uint32_t b_ent_bytes, b_term_bytes, b_stage_bytes;
   uint32_t smem_bytes;

@@ -232,6 +232,8 @@ static void tc_plan_static(const LayerSpec& s, int precision, TcPlan& t) {
   memset(&t, 0, sizeof(t));
   t.NPAD = (int)round_up((size_t)s.cout, 16);
   t.pair_mode = s.cin == 3;
+  t.fold_s = (s.cout == 3 && s.ks == 9 && s.cin != 3 && !getenv("NST_NO_FOLD")) ? 1 : 0;
+  if (t.fold_s) t.NPAD = 32;
   if (t.pair_mode) {
     t.CK = 8; t.planes = 1; t.nchunks = 1;
     t.nent = s.ks * ((s.ks + 1) / 2);
@@ -240,7 +242,7 @@ static void tc_plan_static(const LayerSpec& s, int precision, TcPlan& t) {
     t.CK = (s.cin % 32 == 0) ? 32 : 16;
     t.planes = t.CK / 8;
     t.nchunks = s.cin / t.CK;
-    t.nent = s.ks * s.ks;
+    t.nent = t.fold_s ? s.ks : s.ks * s.ks;
     t.k16_per_ent = t.CK / 16;
   }
   t.is_bf16 = precision == NST_PREC_BF16;
@@ -266,7 +268,9 @@ static bool tc_plan_geometry(const ConvParams& p, TcPlan& t) {
   const int e = p.ks - 1;
   for (int MB = t.MB; MB >= 1; MB = (MB > 1 ? MB / 2 : 0)) {
     const int M = MB * 128;
-    const double mma_cyc = (double)MB * t.nchunks * t.nent * t.k16_per_ent * t.nterms * (t.NPAD / 2.0);
+    // measured tcgen05.mma cost (tools/umma_bench.cu): N=16 39, N=32 40, N=64 48, N=128 64, N=256 128 cycles
+    const double mma_one = t.NPAD >= 128 ? t.NPAD / 2.0 : 32.0 + t.NPAD / 4.0;
+    const double mma_cyc = (double)MB * t.nchunks * t.nent * t.k16_per_ent * t.nterms * mma_one;
     double best = 1e30;
     int bTH = 0, bTW = 0, bP = 0;
     for (int TH = 1; TH <= std::min(64, M); ++TH) {
@@ -294,8 +298,8 @@ static bool tc_plan_geometry(const ConvParams& p, TcPlan& t) {
         for (int r = 0; r < p.ks; ++r) for (int sp = 0; sp < (p.ks + 1) / 2; ++sp) t.ent_off[k++] = r * bP + 2 * sp;
         max_off = e * bP + e + 1;
       } else {
-        for (int r = 0; r < p.ks; ++r) for (int s = 0; s < p.ks; ++s) t.ent_off[k++] = r * bP + s;
-        max_off = e * bP + e;
+        if (t.fold_s) { for (int r = 0; r < p.ks; ++r) t.ent_off[k++] = r * bP; max_off = e * bP; }
+        else { for (int r = 0; r < p.ks; ++r) for (int s = 0; s < p.ks; ++s) t.ent_off[k++] = r * bP + s; max_off = e * bP + e; }
       }
       t.NPOS = std::max(MBu * 128 + max_off + 2, t.halo_h * bP + 2);
     } else {
@@ -315,7 +319,7 @@ static bool tc_plan_geometry(const ConvParams& p, TcPlan& t) {
     t.a_stage_bytes = (uint32_t)round_up((size_t)t.a_term_bytes * t.a_tplanes, 128);
     const int b_total = t.b_stages * (int)t.b_stage_bytes;
     // barriers + TMEM slot + two per-tile source tables [NPOS] (current / next tile) + per-sample norm coefficients [Cin<=256]
-    const int bar_bytes = 640 + 2 * (int)round_up((size_t)t.NPOS * 4, 16) + 256 * 8;
+    const int bar_bytes = 640 + 2 * (int)round_up((size_t)t.NPOS * 4, 16) + 256 * 8 + (t.fold_s ? TC_FOLD_RING_BYTES : 0);
     const int avail = TC_SMEM_LIMIT - b_total - bar_bytes;
     int a_stages = avail / (int)t.a_stage_bytes;
     const int want = t.nchunks == 1 ? 2 : 3;
@@ -366,6 +370,10 @@ static std::vector<uint16_t> tc_pack_weights(const LayerSpec& s, const TcPlan& t
                 const int ci = ch * t.CK + kp * 8 + i;
                 v = w_oihw[(((size_t)n * s.cin + ci) * ks + r) * ks + sx];
               }
+            }
+            if (t.fold_s) {      // column n = s*3 + co of filter row r = ent
+              v = 0.f;
+              if (n < 3 * ks) v = w_oihw[(((size_t)(n % 3) * s.cin + (ch * t.CK + kp * 8 + i)) * ks + ent) * ks + n / 3];
             }
             const uint16_t hi = conv16(v);
             const size_t base = ((size_t)ch * t.ngroups + grp) * stage_elems;
