@@ -298,9 +298,9 @@ __device__ __noinline__ void issue_group_generic(const IssueArgs& a, int k16, in
 // global loads of batch i+1 are issued BEFORE batch i is transformed and written to shared memory,
 // across chunk and tile boundaries, so ~PU*16..32 B per thread are always in flight (the first version
 // waited for every batch: ncu showed the producers stalled on long_scoreboard ~45 % of the time).
-constexpr int PU = 4;
+// PU = halo slots per batch per thread: 8 without a residual operand, 4 with (register budget)
 
-template <bool HAS_RESID>
+template <bool HAS_RESID, int PU>
 struct ProdBatch {
   int ent[PU];
   uint4 a[PU];
@@ -312,8 +312,8 @@ struct ProdCursor {
   uint32_t tb;         // which of the two source tables belongs to `tile`
 };
 
-template <bool HAS_RESID>
-__device__ __forceinline__ void prod_load(ProdBatch<HAS_RESID>& B, const ProdCursor& c, bool valid, const ConvParams& p, const TcPlan& t,
+template <bool HAS_RESID, int PU>
+__device__ __forceinline__ void prod_load(ProdBatch<HAS_RESID, PU>& B, const ProdCursor& c, bool valid, const ConvParams& p, const TcPlan& t,
                                           const int* srcpix, int tbl_stride, int ptid, int pshift, int g, int nitems) {
   const __half* __restrict__ src = (const __half*)p.src;
   const __half* __restrict__ res = (const __half*)p.resid;
@@ -336,7 +336,7 @@ __device__ __forceinline__ void prod_load(ProdBatch<HAS_RESID>& B, const ProdCur
   }
 }
 
-template <bool HAS_RESID>
+template <bool HAS_RESID, int PU>
 __device__ void produce_act16(const ConvParams& p, const TcPlan& t, uint8_t* smem_a, int* srcpix, float2* coeff, uint32_t bar_a_full0,
                               uint32_t bar_a_empty0, unsigned int* err, unsigned long long* prof, int first_tile, int tile_step, int ptid) {
   const int planes = t.planes;
@@ -386,7 +386,7 @@ __device__ void produce_act16(const ConvParams& p, const TcPlan& t, uint8_t* sme
     build_table(c.tile + tile_step, c.tb ^ 1u);
     named_bar_sync(2, TC_PROD_THREADS);
   };
-  auto process = [&](const ProdBatch<HAS_RESID>& B, const ProdCursor& c) {
+  auto process = [&](const ProdBatch<HAS_RESID, PU>& B, const ProdCursor& c) {
     if (c.b == 0) {
       const int c0 = c.ch * t.CK + g * 8;
 #pragma unroll
@@ -440,19 +440,19 @@ __device__ void produce_act16(const ConvParams& p, const TcPlan& t, uint8_t* sme
   cur.tile = first_tile; cur.ch = 0; cur.b = 0; cur.tb = 0u;
   build_table(first_tile, 0u);
   named_bar_sync(2, TC_PROD_THREADS);
-  ProdBatch<HAS_RESID> B0, B1;
-  prod_load<HAS_RESID>(B0, cur, cur.tile < t.num_tiles, p, t, srcpix, tbl_stride, ptid, pshift, g, nitems);
+  ProdBatch<HAS_RESID, PU> B0, B1;
+  prod_load<HAS_RESID, PU>(B0, cur, cur.tile < t.num_tiles, p, t, srcpix, tbl_stride, ptid, pshift, g, nitems);
   while (cur.tile < t.num_tiles) {
     ProdCursor nxt = cur;
     advance(nxt);
     tile_begin(cur);
-    prod_load<HAS_RESID>(B1, nxt, nxt.tile < t.num_tiles, p, t, srcpix, tbl_stride, ptid, pshift, g, nitems);
+    prod_load<HAS_RESID, PU>(B1, nxt, nxt.tile < t.num_tiles, p, t, srcpix, tbl_stride, ptid, pshift, g, nitems);
     process(B0, cur);
     cur = nxt;
     if (cur.tile >= t.num_tiles) break;
     advance(nxt);
     tile_begin(cur);
-    prod_load<HAS_RESID>(B0, nxt, nxt.tile < t.num_tiles, p, t, srcpix, tbl_stride, ptid, pshift, g, nitems);
+    prod_load<HAS_RESID, PU>(B0, nxt, nxt.tile < t.num_tiles, p, t, srcpix, tbl_stride, ptid, pshift, g, nitems);
     process(B1, cur);
     cur = nxt;
   }
@@ -611,28 +611,7 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
     // =========================== epilogue ===========================
     const int quad = warp & 3;                        // TMEM lane quadrant this warp may read
     const int njc = t.NPAD >> 4;
-    float ssum[12], ssq[12];
-#pragma unroll
-    for (int i = 0; i < 12; ++i) { ssum[i] = 0.f; ssq[i] = 0.f; }
     const int my_chan = ((lane & 16) ? 8 : 0) + ((lane & 8) ? 4 : 0) + ((lane & 4) ? 2 : 0) + ((lane & 2) ? 1 : 0);
-    int cur_n = -1;
-    auto flush = [&]() {
-      if (cur_n < 0 || p.out_fmt != OUT_F32_NHWC_STATS) return;
-#pragma unroll
-      for (int jc = 0; jc < 12; ++jc) {
-        if (jc < njc) {
-          const int c = jc * 16 + my_chan;
-          if ((lane & 1) == 0 && c < p.Cout) {
-            double* st = p.out_stats + ((size_t)cur_n * p.Cout + c) * 2;
-            atomicAdd(st, (double)ssum[jc]);
-            atomicAdd(st + 1, (double)ssq[jc]);
-          }
-          ssum[jc] = 0.f; ssq[jc] = 0.f;
-        }
-      }
-    };
-    uint32_t it = 0;
-    WaitProf wprof; wprof.init(args.prof);
     if (t.fold_s) {
       // Image layer with the horizontal taps folded into N:  TMEM holds T[m][s*3+co] = sum_{r,ci} in[m + r*P][ci] w[co][ci][r][s];
       // out[m][co] = sum_s T[m + s][s*3 + co].  Rows are exchanged through a two-block ring in shared memory: block mb is
@@ -677,80 +656,110 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
         }
       }
       wprof.flush(2, warp == TC_FIRST_EPI_WARP && lane == 0);
-    } else
-    for (int tile = first_tile; tile < ((t.dbg & 32) ? 0 : t.num_tiles); tile += tile_step, ++it) {
-      const TileCoord tc = decode_tile(t, tile);
-      if (tc.n != cur_n) { flush(); cur_n = tc.n; }
-      const uint32_t buf = it & 1u;
-      mbar_wait(ACC_FULL(buf), (it >> 1) & 1u, err, 5, wprof);
-      tc_fence_after();
-      for (int mb = 0; mb < ((t.dbg & 4) ? 0 : t.MB); ++mb) {
-        const int m = mb * 128 + quad * 32 + lane;
-        const int ty = m / t.P;
-        const int tx = m - ty * t.P;
-        const int oy = tc.ty0 + ty, ox = tc.tx0 + tx;
-        const bool valid = ty < t.TH && tx < t.TW && oy < p.Ho && ox < p.Wo;
-        const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + buf * (uint32_t)(t.MB * t.NPAD) + (uint32_t)(mb * t.NPAD);
+    } else {
+      // Per-warp running (sum, sum of squares) of every output channel live in shared memory ([NPAD][2] floats per
+      // warp) so neither loop below needs unrolling; they go to the global double table when the sample changes.
+      float* wstat = fold_ring + (size_t)(warp - TC_FIRST_EPI_WARP) * t.NPAD * 2;
+      for (int c = lane; c < t.NPAD * 2; c += 32) wstat[c] = 0.f;
+      __syncwarp();
+      int cur_n = -1;
+      auto flush = [&]() {
+        if (cur_n < 0 || p.out_fmt != OUT_F32_NHWC_STATS) return;
+        __syncwarp();
+        for (int c = lane; c < p.Cout; c += 32) {
+          double* st = p.out_stats + ((size_t)cur_n * p.Cout + c) * 2;
+          atomicAdd(st, (double)wstat[2 * c]);
+          atomicAdd(st + 1, (double)wstat[2 * c + 1]);
+          wstat[2 * c] = 0.f; wstat[2 * c + 1] = 0.f;
+        }
+        __syncwarp();
+      };
+      const float inv_p = 1.0f / (float)t.P;
+      uint32_t it = 0;
+      WaitProf wprof; wprof.init(args.prof);
+      for (int tile = first_tile; tile < ((t.dbg & 32) ? 0 : t.num_tiles); tile += tile_step, ++it) {
+        const TileCoord tc = decode_tile(t, tile);
+        if (tc.n != cur_n) { flush(); cur_n = tc.n; }
+        const uint32_t buf = it & 1u;
+        mbar_wait(ACC_FULL(buf), (it >> 1) & 1u, err, 5, wprof);
+        tc_fence_after();
+        const uint32_t tbase = tmem_base + ((uint32_t)(quad * 32) << 16) + buf * (uint32_t)(t.MB * t.NPAD);
         if (p.out_fmt == OUT_F32_NHWC_STATS) {
-          const size_t orow_idx = (((size_t)tc.n * p.Ho + oy) * p.Wo + ox) * p.Cout;
-          float* orow = (float*)p.out + orow_idx;
-          __half* orow16 = (__half*)p.out + orow_idx;
+          const int nmb = (t.dbg & 4) ? 0 : t.MB;
+          for (int jc = 0; jc < njc; ++jc) {
+            // 16 channels at a time: rows of all M blocks are accumulated per lane first, then ONE butterfly
+            // (16 -> 8 -> 4 -> 2 -> 1 live channels per step) reduces over the 32 lanes.
+            float s[16], q[16];
 #pragma unroll
-          for (int jc = 0; jc < 12; ++jc) {
-            if (jc < njc) {
+            for (int i = 0; i < 16; ++i) { s[i] = 0.f; q[i] = 0.f; }
+            for (int mb = 0; mb < nmb; ++mb) {
+              const int m = mb * 128 + quad * 32 + lane;
+              const int ty = (int)(((float)m + 0.5f) * inv_p);
+              const int tx = m - ty * t.P;
+              const int oy = tc.ty0 + ty, ox = tc.tx0 + tx;
+              const bool valid = ty < t.TH && tx < t.TW && oy < p.Ho && ox < p.Wo;
               float v[16];
-              if (t.dbg & 512) { for (int i = 0; i < 16; ++i) v[i] = 0.f; } else
-              tmem_ld16(taddr + (uint32_t)(jc * 16), v);
-              if (valid && !(t.dbg & 128)) {
+              tmem_ld16(tbase + (uint32_t)(mb * t.NPAD + jc * 16), v);
+              if (valid) {
+                const size_t oidx = (((size_t)tc.n * p.Ho + oy) * p.Wo + ox) * p.Cout + jc * 16;
                 if (p.act16) {
                   uint32_t h[8];
 #pragma unroll
                   for (int i = 0; i < 8; ++i) h[i] = pack2(v[2 * i], v[2 * i + 1], 0);
-                  uint4* o4 = reinterpret_cast<uint4*>(orow16 + jc * 16);
+                  uint4* o4 = reinterpret_cast<uint4*>((__half*)p.out + oidx);
                   o4[0] = make_uint4(h[0], h[1], h[2], h[3]);
                   o4[1] = make_uint4(h[4], h[5], h[6], h[7]);
                 } else {
-                  float4* o4 = reinterpret_cast<float4*>(orow + jc * 16);
+                  float4* o4 = reinterpret_cast<float4*>((float*)p.out + oidx);
                   o4[0] = make_float4(v[0], v[1], v[2], v[3]);
                   o4[1] = make_float4(v[4], v[5], v[6], v[7]);
                   o4[2] = make_float4(v[8], v[9], v[10], v[11]);
                   o4[3] = make_float4(v[12], v[13], v[14], v[15]);
                 }
+#pragma unroll
+                for (int i = 0; i < 16; ++i) { s[i] += v[i]; q[i] = fmaf(v[i], v[i], q[i]); }
               }
-              // per-channel sum / sum of squares over the 32 rows of this warp: butterfly that halves
-              // the number of live channels per step (16 -> 8 -> 4 -> 2 -> 1), then one pair add.
-              if (t.dbg & 256) continue;
-              float s[16], q[16];
+            }
+            if (jc == njc - 1 && nmb > 0) { tc_fence_before(); mbar_arrive(ACC_EMPTY(buf)); }
 #pragma unroll
-              for (int i = 0; i < 16; ++i) { s[i] = valid ? v[i] : 0.f; q[i] = s[i] * s[i]; }
+            for (int w = 8, off = 16; w >= 1; w >>= 1, off >>= 1) {
+              const bool up = (lane & off) != 0;
 #pragma unroll
-              for (int w = 8, off = 16; w >= 1; w >>= 1, off >>= 1) {
-                const bool up = (lane & off) != 0;
-#pragma unroll
-                for (int i = 0; i < w; ++i) {
-                  const float send_s = up ? s[i] : s[i + w];
-                  const float send_q = up ? q[i] : q[i + w];
-                  const float keep_s = up ? s[i + w] : s[i];
-                  const float keep_q = up ? q[i + w] : q[i];
-                  s[i] = keep_s + __shfl_xor_sync(0xffffffffu, send_s, off);
-                  q[i] = keep_q + __shfl_xor_sync(0xffffffffu, send_q, off);
-                }
+              for (int i = 0; i < w; ++i) {
+                const float send_s = up ? s[i] : s[i + w];
+                const float send_q = up ? q[i] : q[i + w];
+                const float keep_s = up ? s[i + w] : s[i];
+                const float keep_q = up ? q[i + w] : q[i];
+                s[i] = keep_s + __shfl_xor_sync(0xffffffffu, send_s, off);
+                q[i] = keep_q + __shfl_xor_sync(0xffffffffu, send_q, off);
               }
-              ssum[jc] += s[0] + __shfl_xor_sync(0xffffffffu, s[0], 1);
-              ssq[jc] += q[0] + __shfl_xor_sync(0xffffffffu, q[0], 1);
+            }
+            const float ts = s[0] + __shfl_xor_sync(0xffffffffu, s[0], 1);
+            const float tq = q[0] + __shfl_xor_sync(0xffffffffu, q[0], 1);
+            if ((lane & 1) == 0) {
+              float2* w2 = reinterpret_cast<float2*>(wstat) + jc * 16 + my_chan;
+              float2 cur = *w2;
+              cur.x += ts; cur.y += tq;
+              *w2 = cur;
             }
           }
+          if (njc == 0 || nmb == 0) { tc_fence_before(); mbar_arrive(ACC_EMPTY(buf)); }
         } else {
-          float v[16];
-          tmem_ld16(taddr, v);
-          if (valid) store_image(p, tc.n, oy, ox, v[0] + p.bias[0], v[1] + p.bias[1], v[2] + p.bias[2]);
+          for (int mb = 0; mb < t.MB; ++mb) {
+            const int m = mb * 128 + quad * 32 + lane;
+            const int ty = m / t.P, tx = m - ty * t.P;
+            const int oy = tc.ty0 + ty, ox = tc.tx0 + tx;
+            float v[16];
+            tmem_ld16(tbase + (uint32_t)(mb * t.NPAD), v);
+            if (ty < t.TH && tx < t.TW && oy < p.Ho && ox < p.Wo) store_image(p, tc.n, oy, ox, v[0] + p.bias[0], v[1] + p.bias[1], v[2] + p.bias[2]);
+          }
+          tc_fence_before();
+          mbar_arrive(ACC_EMPTY(buf));
         }
       }
-      tc_fence_before();
-      mbar_arrive(ACC_EMPTY(buf));
+      flush();
+      wprof.flush(2, warp == TC_FIRST_EPI_WARP && lane == 0);
     }
-    flush();
-    wprof.flush(2, warp == TC_FIRST_EPI_WARP && lane == 0);
   } else {
     // =========================== operand producers ===========================
     const int ptid = threadIdx.x - TC_FIRST_PROD_WARP * 32;
@@ -770,8 +779,8 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
     int cur_n = -1;
     if (t.dbg & 16) {
     } else if (nhwc && p.act16) {
-      if (has_resid) produce_act16<true>(p, t, smem_a, srcpix, coeff, A_FULL(0), A_EMPTY(0), err, args.prof, first_tile, tile_step, ptid);
-      else produce_act16<false>(p, t, smem_a, srcpix, coeff, A_FULL(0), A_EMPTY(0), err, args.prof, first_tile, tile_step, ptid);
+      if (has_resid) produce_act16<true, 4>(p, t, smem_a, srcpix, coeff, A_FULL(0), A_EMPTY(0), err, args.prof, first_tile, tile_step, ptid);
+      else produce_act16<false, 4>(p, t, smem_a, srcpix, coeff, A_FULL(0), A_EMPTY(0), err, args.prof, first_tile, tile_step, ptid);
     } else
     for (int tile = first_tile; tile < t.num_tiles; tile += tile_step) {
       const TileCoord tc = decode_tile(t, tile);

@@ -319,7 +319,7 @@ static bool tc_plan_geometry(const ConvParams& p, TcPlan& t) {
     t.a_stage_bytes = (uint32_t)round_up((size_t)t.a_term_bytes * t.a_tplanes, 128);
     const int b_total = t.b_stages * (int)t.b_stage_bytes;
     // barriers + TMEM slot + two per-tile source tables [NPOS] (current / next tile) + per-sample norm coefficients [Cin<=256]
-    const int bar_bytes = 640 + 2 * (int)round_up((size_t)t.NPOS * 4, 16) + 256 * 8 + (t.fold_s ? TC_FOLD_RING_BYTES : 0);
+    const int bar_bytes = 640 + 2 * (int)round_up((size_t)t.NPOS * 4, 16) + 256 * 8 + (t.fold_s ? TC_FOLD_RING_BYTES : 4 * t.NPAD * 8);   // + epilogue scratch: fold ring, or per-warp channel statistics
     const int avail = TC_SMEM_LIMIT - b_total - bar_bytes;
     int a_stages = avail / (int)t.a_stage_bytes;
     const int want = t.nchunks == 1 ? 2 : 3;
