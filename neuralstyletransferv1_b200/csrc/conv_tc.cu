@@ -330,8 +330,10 @@ __device__ __forceinline__ void prod_load(ProdBatch<HAS_RESID, PU>& B, const Pro
     if (HAS_RESID) B.r[u] = make_uint4(0u, 0u, 0u, 0u);
     if (B.ent[u] >= 0) {
       const size_t off = (size_t)(B.ent[u] & (SIDE_BIT - 1)) * p.Cin + c0;
+      if (!(t.dbg & 1024)) {
       B.a[u] = __ldg(reinterpret_cast<const uint4*>(src + off));
       if (HAS_RESID) B.r[u] = __ldg(reinterpret_cast<const uint4*>(res + off));
+      }
     }
   }
 }
@@ -414,7 +416,7 @@ __device__ void produce_act16(const ConvParams& p, const TcPlan& t, uint8_t* sme
           v0 = fmaxf(v0, lo2); v1 = fmaxf(v1, lo2);
           hi[i] = pack2(v0, v1, is_bf16);
         }
-        if (e & SIDE_BIT) {
+        if ((e & SIDE_BIT) && !(t.dbg & 4096)) {
           // the materialised block input is stored as fp16 -- the same rounding the MMA operand gets
           uint32_t sv[4];
           if (is_bf16) {
@@ -427,7 +429,7 @@ __device__ void produce_act16(const ConvParams& p, const TcPlan& t, uint8_t* sme
           *reinterpret_cast<uint4*>(side + (size_t)(e & (SIDE_BIT - 1)) * p.Cin + c0) = make_uint4(sv[0], sv[1], sv[2], sv[3]);
         }
       }
-      *reinterpret_cast<uint4*>(plane_hi + (size_t)q * 16) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+      if (!(t.dbg & 2048)) *reinterpret_cast<uint4*>(plane_hi + (size_t)q * 16) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
     }
     if (c.b == nB - 1) {
       fence_proxy_async_smem();
