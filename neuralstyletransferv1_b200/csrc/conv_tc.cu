@@ -534,6 +534,69 @@ __device__ __noinline__ void mma_role(const TcPlan& t, const MmaCtx c) {
   wprof.flush(1, (threadIdx.x & 31) == 0);
 }
 
+// Sub-pixel (phase) layers: every entry multiplies its own accumulator column range [col, col+n) with its own N.
+__device__ __noinline__ void mma_role_phase(const TcPlan& t, const MmaCtx c) {
+  const uint32_t fmt = t.is_bf16 ? 1u : 0u;
+  const uint32_t idesc0 = (1u << 4) | (fmt << 7) | (fmt << 10) | ((uint32_t)(128 >> 4) << 24);
+  const uint32_t a_lo_base = ((c.smem_a >> 4) & 0x3FFFu) | ((t.a_plane_bytes >> 4) << 16);
+  const uint32_t b_addr_base = (c.smem_b >> 4) & 0x3FFFu;
+  const uint32_t a_kstep16 = (2u * t.a_plane_bytes) >> 4;
+  const uint32_t a_stage16 = t.a_stage_bytes >> 4, b_stage16 = t.b_stage_bytes >> 4;
+  const int MB = t.MB, NPAD = t.NPAD, k16 = t.k16_per_ent;
+  const int nchunks = t.nchunks, ngroups = t.ngroups, num_tiles = t.num_tiles;
+  const uint32_t a_stages = (uint32_t)t.a_stages, b_stages = (uint32_t)t.b_stages;
+  const uint32_t A_FULL0 = c.bar0, A_EMPTY0 = c.bar0 + 8u * TC_MAX_A_STAGES, B_FULL0 = c.bar0 + 8u * (2 * TC_MAX_A_STAGES),
+                 B_EMPTY0 = B_FULL0 + 8u * TC_MAX_B_STAGES, ACC_FULL0 = B_FULL0 + 8u * (2 * TC_MAX_B_STAGES), ACC_EMPTY0 = ACC_FULL0 + 16u;
+  const uint32_t* ent_info = c.ent_tab + 32;
+  int gfirst[5];
+#pragma unroll
+  for (int i = 0; i < 5; ++i) gfirst[i] = t.grp_first[i];
+  WaitProf wprof; wprof.init(c.prof);
+  uint32_t sa = 0, pa = 0, sb = 0, pb = 0, it = 0;
+  for (int tile = c.first_tile; tile < num_tiles; tile += c.tile_step, ++it) {
+    const uint32_t buf = it & 1u;
+    mbar_wait(ACC_EMPTY0 + 8u * buf, ((it >> 1) & 1u) ^ 1u, c.err, 2, wprof);
+    tc_fence_after();
+    const uint32_t tmem_acc = c.tmem_base + buf * (uint32_t)(MB * NPAD);
+    for (int ch = 0; ch < nchunks; ++ch) {
+      mbar_wait(A_FULL0 + 8u * sa, pa, c.err, 3, wprof);
+      tc_fence_after();
+      const uint32_t a_stage_lo = a_lo_base + sa * a_stage16;
+      for (int g = 0; g < ngroups; ++g) {
+        mbar_wait(B_FULL0 + 8u * sb, pb, c.err, 4, wprof);
+        tc_fence_after();
+        if (elect_one_sync()) {
+          const uint32_t b_stage_addr = b_addr_base + sb * b_stage16;
+          const int e1 = g == 0 ? gfirst[1] : gfirst[2];
+          for (int e = (g == 0 ? gfirst[0] : gfirst[1]); e < e1; ++e) {
+            const uint32_t info = ent_info[e];
+            const uint32_t col = info & 511u, n = ((info >> 9) & 31u) * 16u;
+            const uint32_t a_lo = a_stage_lo + c.ent_tab[e];
+            const uint32_t b_lo = (b_stage_addr + (info >> 14)) | (n << 16);          // LBO = n*16 bytes
+            const uint32_t idesc = idesc0 | ((n >> 3) << 17);
+            const uint32_t acc = (ch > 0 || e > 0) ? 1u : 0u;
+            for (int j = 0; j < k16; ++j) {
+              const uint64_t bdesc = ((uint64_t)DESC_HI << 32) | (b_lo + (uint32_t)j * 2u * n);
+              for (int mb = 0; mb < MB; ++mb)
+                umma_f16(tmem_acc + (uint32_t)(mb * NPAD) + col, ((uint64_t)DESC_HI << 32) | (a_lo + (uint32_t)j * a_kstep16 + (uint32_t)mb * 128u), bdesc,
+                         idesc, (j > 0) ? 1u : acc);
+            }
+          }
+          umma_commit(B_EMPTY0 + 8u * sb);
+        }
+        __syncwarp();
+        if (++sb == b_stages) { sb = 0; pb ^= 1u; }
+      }
+      if (elect_one_sync()) umma_commit(A_EMPTY0 + 8u * sa);
+      __syncwarp();
+      if (++sa == a_stages) { sa = 0; pa ^= 1u; }
+    }
+    if (elect_one_sync()) umma_commit(ACC_FULL0 + 8u * buf);
+    __syncwarp();
+  }
+  wprof.flush(1, (threadIdx.x & 31) == 0);
+}
+
 constexpr int NBARS = 2 * TC_MAX_A_STAGES + 2 * TC_MAX_B_STAGES + 4;
 
 __global__ void __launch_bounds__(TC_THREADS, 1)
@@ -600,9 +663,11 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
   } else if (warp == 1) {
     // =========================== MMA issuer ===========================
     for (int i = lane; i < t.nent; i += 32) ent_tab[i] = (uint32_t)t.ent_off[i];
+    if (t.phase_mode && lane < 16) ent_tab[32 + lane] = t.ent_info[lane];
     __syncwarp();
     const MmaCtx mc = {smem_u32(smem_a), smem_u32(smem_b), bar0, tmem_base, ent_tab, err, args.prof, first_tile, tile_step};
-    if (t.nterms == 1 && t.k16_per_ent == 2 && t.MB == 2) mma_role<2, 2>(t, mc);
+    if (t.phase_mode) mma_role_phase(t, mc);
+    else if (t.nterms == 1 && t.k16_per_ent == 2 && t.MB == 2) mma_role<2, 2>(t, mc);
     else if (t.nterms == 1 && t.k16_per_ent == 2 && t.MB == 4) mma_role<2, 4>(t, mc);
     else if (t.nterms == 1 && t.k16_per_ent == 2 && t.MB == 8) mma_role<2, 8>(t, mc);
     else if (t.nterms == 1 && t.k16_per_ent == 2 && t.MB == 1) mma_role<2, 1>(t, mc);
@@ -694,6 +759,8 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
             float s[16], q[16];
 #pragma unroll
             for (int i = 0; i < 16; ++i) { s[i] = 0.f; q[i] = 0.f; }
+            const int ph = p.phase_mode ? (jc * 16) / p.Cout : 0;           // sub-pixel layers: column = phase*Cout + co
+            const int co0 = jc * 16 - ph * p.Cout;
             for (int mb = 0; mb < nmb; ++mb) {
               const int m = mb * 128 + quad * 32 + lane;
               const int ty = (int)(((float)m + 0.5f) * inv_p);
@@ -703,7 +770,9 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
               float v[16];
               tmem_ld16(tbase + (uint32_t)(mb * t.NPAD + jc * 16), v);
               if (valid) {
-                const size_t oidx = (((size_t)tc.n * p.Ho + oy) * p.Wo + ox) * p.Cout + jc * 16;
+                size_t oidx;
+                if (p.phase_mode) oidx = (((size_t)tc.n * (2 * p.Ho) + 2 * oy + (ph >> 1)) * (size_t)(2 * p.Wo) + 2 * ox + (ph & 1)) * p.Cout + co0;
+                else oidx = (((size_t)tc.n * p.Ho + oy) * p.Wo + ox) * p.Cout + jc * 16;
                 if (p.act16) {
                   uint32_t h[8];
 #pragma unroll
@@ -739,7 +808,7 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
             const float ts = s[0] + __shfl_xor_sync(0xffffffffu, s[0], 1);
             const float tq = q[0] + __shfl_xor_sync(0xffffffffu, q[0], 1);
             if ((lane & 1) == 0) {
-              float2* w2 = reinterpret_cast<float2*>(wstat) + jc * 16 + my_chan;
+              float2* w2 = reinterpret_cast<float2*>(wstat) + co0 + my_chan;
               float2 cur = *w2;
               cur.x += ts; cur.y += tq;
               *w2 = cur;

@@ -45,6 +45,11 @@ struct TcPlan {
   uint32_t b_ent_bytes, b_term_bytes, b_stage_bytes;
   uint32_t smem_bytes;
   int ent_off[TC_MAX_ENT];  // A position offset of each entry
+  // sub-pixel (phase) layers: entry e multiplies only the accumulator columns [col, col + n) -- the phases its tap feeds.
+  // ent_info[e] = col | (n / 16) << 9 | (B offset inside the weight stage, 16-byte units) << 14; 0 entries = plain layer
+  int phase_mode;
+  int grp_first[5];         // first entry of each weight stage (phase layers: stages hold different entry counts)
+  uint32_t ent_info[16];
 };
 
 struct TcArgs {

@@ -228,8 +228,49 @@ static bool tc_supported(const LayerSpec& s) {
   return true;
 }
 
+// Sub-pixel form of  nearest-upsample x2 -> ReflectionPad2d(1) -> Conv2d(k3)  (transformer_net.py:79-99, model.py:96-99):
+// output pixel (2i+a, 2j+b) only sees the 2x2 low-res neighbourhood of (i,j), so the layer is a 3x3 conv over the LOW-RES
+// tensor with replicate padding and N = 4 phases x Cout columns, where tap (r,s) feeds only some phases.  Entry table:
+// low-res tap (r,s), first phase (= a*2+b), number of adjacent phases.  Entry 0 covers every column (it initialises the accumulator).
+static const int PH_NENT = 11;
+static const int PH_R[PH_NENT]  = {1, 0, 2, 1, 1, 1, 1, 0, 0, 2, 2};
+static const int PH_S[PH_NENT]  = {1, 1, 1, 0, 0, 2, 2, 0, 2, 0, 2};
+static const int PH_P0[PH_NENT] = {0, 0, 2, 0, 2, 1, 3, 0, 1, 2, 3};
+static const int PH_NP[PH_NENT] = {4, 2, 2, 1, 1, 1, 1, 1, 1, 1, 1};
+// original taps r' that land on low-res tap r for row/column phase a:  a=0: {0} {1,2} {};  a=1: {} {0,1} {2}
+static bool ph_hits(int a, int r, int rp) {
+  if (a == 0) return (r == 0 && rp == 0) || (r == 1 && rp >= 1);
+  return (r == 1 && rp <= 1) || (r == 2 && rp == 2);
+}
+static bool phase_eligible(const LayerSpec& s, int precision) {
+  return s.map_mode == MAP_UP2 && s.pad_mode == PAD_REFLECT && s.ks == 3 && s.stride == 1 && s.cout % 16 == 0 && 4 * s.cout <= 256 &&
+         s.cin % 16 == 0 && precision != NST_PREC_F16X3 && !getenv("NST_NO_PHASE");
+}
+
 static void tc_plan_static(const LayerSpec& s, int precision, TcPlan& t) {
   memset(&t, 0, sizeof(t));
+  if (phase_eligible(s, precision)) {
+    t.phase_mode = 1;
+    t.NPAD = 4 * s.cout;
+    t.CK = (s.cin % 32 == 0) ? 32 : 16;
+    t.planes = t.CK / 8; t.nchunks = s.cin / t.CK; t.nent = PH_NENT; t.k16_per_ent = t.CK / 16;
+    t.is_bf16 = precision == NST_PREC_BF16;
+    t.nterms = 1; t.a_tplanes = 1; t.b_tplanes = 1;
+    t.ngroups = 2; t.tg = 8;
+    t.grp_first[0] = 0; t.grp_first[1] = 3; t.grp_first[2] = PH_NENT;
+    uint32_t grp_bytes[2] = {0, 0};
+    for (int e = 0; e < PH_NENT; ++e) {
+      const int g = e < 3 ? 0 : 1;
+      const int n = PH_NP[e] * s.cout;
+      t.ent_info[e] = (uint32_t)(PH_P0[e] * s.cout) | ((uint32_t)(n / 16) << 9) | ((grp_bytes[g] / 16u) << 14);
+      grp_bytes[g] += (uint32_t)(t.planes * n * 16);
+    }
+    t.b_ent_bytes = (uint32_t)(t.planes * t.NPAD * 16);
+    t.b_stage_bytes = t.b_term_bytes = std::max(grp_bytes[0], grp_bytes[1]);
+    t.b_stages = t.b_stage_bytes > 24576 ? 2 : 3;
+    t.MB = std::max(1, 256 / t.NPAD);
+    return;
+  }
   t.NPAD = (int)round_up((size_t)s.cout, 16);
   t.pair_mode = s.cin == 3;
   t.fold_s = (s.cout == 3 && s.ks == 9 && s.cin != 3 && !getenv("NST_NO_FOLD")) ? 1 : 0;
@@ -270,7 +311,8 @@ static bool tc_plan_geometry(const ConvParams& p, TcPlan& t) {
     const int M = MB * 128;
     // measured tcgen05.mma cost (tools/umma_bench.cu): N=16 39, N=32 40, N=64 48, N=128 64, N=256 128 cycles
     const double mma_one = t.NPAD >= 128 ? t.NPAD / 2.0 : 32.0 + t.NPAD / 4.0;
-    const double mma_cyc = (double)MB * t.nchunks * t.nent * t.k16_per_ent * t.nterms * mma_one;
+    double mma_cyc = (double)MB * t.nchunks * t.nent * t.k16_per_ent * t.nterms * mma_one;
+    if (t.phase_mode) mma_cyc = (double)MB * t.nchunks * t.k16_per_ent * (t.NPAD * 2.5);
     double best = 1e30;
     int bTH = 0, bTW = 0, bP = 0;
     for (int TH = 1; TH <= std::min(64, M); ++TH) {
@@ -298,7 +340,8 @@ static bool tc_plan_geometry(const ConvParams& p, TcPlan& t) {
         for (int r = 0; r < p.ks; ++r) for (int sp = 0; sp < (p.ks + 1) / 2; ++sp) t.ent_off[k++] = r * bP + 2 * sp;
         max_off = e * bP + e + 1;
       } else {
-        if (t.fold_s) { for (int r = 0; r < p.ks; ++r) t.ent_off[k++] = r * bP; max_off = e * bP; }
+        if (t.phase_mode) { for (int i = 0; i < PH_NENT; ++i) t.ent_off[k++] = PH_R[i] * bP + PH_S[i]; max_off = e * bP + e; }
+        else if (t.fold_s) { for (int r = 0; r < p.ks; ++r) t.ent_off[k++] = r * bP; max_off = e * bP; }
         else { for (int r = 0; r < p.ks; ++r) for (int s = 0; s < p.ks; ++s) t.ent_off[k++] = r * bP + s; max_off = e * bP + e; }
       }
       t.NPOS = std::max(MBu * 128 + max_off + 2, t.halo_h * bP + 2);
@@ -342,6 +385,25 @@ static bool tc_plan_geometry(const ConvParams& p, TcPlan& t) {
 static std::vector<uint16_t> tc_pack_weights(const LayerSpec& s, const TcPlan& t, const std::vector<float>& w_oihw) {
   const size_t stage_elems = t.b_stage_bytes / 2;
   std::vector<uint16_t> out((size_t)t.nchunks * t.ngroups * stage_elems, 0);
+  if (t.phase_mode) {
+    // entry e at [chunk][stage g][B offset]: [8-channel plane][n = (phase - phase0)*Cout + co][8] of the pre-summed phase weights
+    for (int ch = 0; ch < t.nchunks; ++ch) for (int e = 0; e < PH_NENT; ++e) {
+      const int g = e < t.grp_first[1] ? 0 : 1;
+      const int n_e = PH_NP[e] * s.cout;
+      const size_t base = ((size_t)ch * t.ngroups + g) * stage_elems + (size_t)(t.ent_info[e] >> 14) * 8;
+      for (int kp = 0; kp < t.planes; ++kp) for (int n = 0; n < n_e; ++n) for (int i = 0; i < 8; ++i) {
+        const int ph = PH_P0[e] + n / s.cout, co = n % s.cout, ci = ch * t.CK + kp * 8 + i;
+        const int a = ph >> 1, b = ph & 1;
+        float v = 0.f;
+        for (int rp = 0; rp < 3; ++rp) for (int sp = 0; sp < 3; ++sp)
+          if (ph_hits(a, PH_R[e], rp) && ph_hits(b, PH_S[e], sp)) v += w_oihw[(((size_t)co * s.cin + ci) * 3 + rp) * 3 + sp];
+        uint16_t u;
+        if (t.is_bf16) { __nv_bfloat16 hv = __float2bfloat16_rn(v); memcpy(&u, &hv, 2); } else { __half hv = __float2half_rn(v); memcpy(&u, &hv, 2); }
+        out[base + ((size_t)kp * n_e + n) * 8 + i] = u;
+      }
+    }
+    return out;
+  }
   auto conv16 = [&](float v) -> uint16_t {
     if (t.is_bf16) { __nv_bfloat16 h = __float2bfloat16_rn(v); uint16_t u; memcpy(&u, &h, 2); return u; }
     __half h = __float2half_rn(v); uint16_t u; memcpy(&u, &h, 2); return u;
@@ -609,7 +671,13 @@ static int make_plan(nst_handle* h, int N, int H, int W) {
     lp.use_tc = h->dev[li].tc_ok && ((h->tc_layer_mask >> li) & 1ull);
     if (lp.use_tc) {
       lp.t = h->dev[li].tc_static;
-      if (!tc_plan_geometry(p, lp.t)) lp.use_tc = false;
+      if (lp.t.phase_mode) {
+        // tile over the low-res grid; the epilogue scatters the four phases into the [N, 2Hs, 2Ws, Cout] output
+        ConvParams q = p;
+        q.phase_mode = 1; q.map_mode = MAP_IDENTITY; q.pad_mode = PAD_REPLICATE;
+        q.Hc = p.Hs; q.Wc = p.Ws; q.Ho = p.Hs; q.Wo = p.Ws;
+        if (tc_plan_geometry(q, lp.t)) p = q; else lp.use_tc = false;
+      } else if (!tc_plan_geometry(p, lp.t)) lp.use_tc = false;
     }
   }
   size_t off = 0;

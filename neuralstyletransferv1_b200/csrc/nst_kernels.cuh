@@ -20,7 +20,7 @@ namespace nst {
 enum InFmt { IN_F32_NHWC = 0, IN_F32_NCHW3 = 1, IN_U8_NHWC3 = 2 };
 enum OutFmt { OUT_F32_NHWC_STATS = 0, OUT_F32_NCHW3 = 1, OUT_U8_NHWC3 = 2 };
 enum MapMode { MAP_IDENTITY = 0, MAP_UP2 = 1, MAP_ZERO_INSERT2 = 2, MAP_PREPAD_REFLECT = 3 };
-enum PadMode { PAD_REFLECT = 0, PAD_ZERO = 1 };
+enum PadMode { PAD_REFLECT = 0, PAD_ZERO = 1, PAD_REPLICATE = 2 };
 
 constexpr float kInEps = 1e-5f;   // torch.nn.InstanceNorm2d default eps
 
@@ -46,6 +46,8 @@ struct ConvParams {
   // ---- output ----
   int Ho, Wo, Cout;         // produced extent
   int oy_off, ox_off;       // produced (0,0) sits at this conv-output coordinate (NST crop)
+  int phase_mode;           // sub-pixel form of upsample x2 + conv3: (Ho, Wo) is the LOW-RES tile grid, GEMM column = phase*Cout + co,
+                            // phase (a,b) of grid position (i,j) is output pixel (2i+a, 2j+b) of the [N, 2Ho, 2Wo, Cout] tensor
   int out_fmt;
   void* out;                // OUT_F32_NHWC_STATS: float [N,Ho,Wo,Cout]; OUT_F32_NCHW3: float [N,3,Ho,Wo]; OUT_U8: u8 [N,Ho,Wo,3]
   double* out_stats;        // [N][Cout][2]
@@ -72,6 +74,8 @@ __device__ __forceinline__ int map_coord(int u, int Hc, int Hs, int map_mode, in
     if (u < 0) u = -u;
     if (u >= Hc) u = 2 * (Hc - 1) - u;
     u = max(0, min(u, Hc - 1));            // rows of partial tiles beyond the image: any finite value
+  } else if (pad_mode == PAD_REPLICATE) {
+    u = max(0, min(u, Hc - 1));
   } else {
     if (u < 0 || u >= Hc) return -1;
   }
