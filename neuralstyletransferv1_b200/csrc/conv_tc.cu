@@ -535,6 +535,35 @@ __device__ __noinline__ void mma_role(const TcPlan& t, const MmaCtx c) {
 }
 
 // Sub-pixel (phase) layers: every entry multiplies its own accumulator column range [col, col+n) with its own N.
+// The entry table is compile-time (it mirrors PH_* in nst_api.cu), so a weight stage unrolls into straight-line
+// uniform-register code; a runtime-table loop cost ~290 cycles per MMA (descriptors built in vector registers).
+template <int K16, int MB, int E0, int E1>
+__device__ __forceinline__ void issue_phase(uint32_t tmem_acc, uint32_t a_stage_lo, uint32_t b_stage_addr, uint32_t a_kstep16, uint32_t P,
+                                            uint32_t cout, uint32_t planes, uint32_t npad, uint32_t idesc0, uint32_t acc_first) {
+  constexpr int R[11]  = {1, 0, 2, 1, 1, 1, 1, 0, 0, 2, 2};
+  constexpr int S[11]  = {1, 1, 1, 0, 0, 2, 2, 0, 2, 0, 2};
+  constexpr int P0[11] = {0, 0, 2, 0, 2, 1, 3, 0, 1, 2, 3};
+  constexpr int NP[11] = {4, 2, 2, 1, 1, 1, 1, 1, 1, 1, 1};
+  uint32_t units = 0;
+#pragma unroll
+  for (int e = E0; e < E1; ++e) {
+    const uint32_t n = (uint32_t)NP[e] * cout, col = (uint32_t)P0[e] * cout;
+    const uint32_t a_lo = a_stage_lo + (uint32_t)R[e] * P + (uint32_t)S[e];
+    const uint32_t b_lo = (b_stage_addr + units * planes * cout) | (n << 16);           // LBO = n*16 bytes
+    const uint32_t idesc = idesc0 | ((n >> 3) << 17);
+#pragma unroll
+    for (int j = 0; j < K16; ++j) {
+      const uint64_t bdesc = ((uint64_t)DESC_HI << 32) | (b_lo + (uint32_t)j * 2u * n);
+#pragma unroll
+      for (int mb = 0; mb < MB; ++mb)
+        umma_f16(tmem_acc + (uint32_t)mb * npad + col, ((uint64_t)DESC_HI << 32) | (a_lo + (uint32_t)j * a_kstep16 + (uint32_t)mb * 128u), bdesc, idesc,
+                 (e == 0 && j == 0) ? acc_first : 1u);
+    }
+    units += (uint32_t)NP[e];
+  }
+}
+
+template <int K16, int MB_>
 __device__ __noinline__ void mma_role_phase(const TcPlan& t, const MmaCtx c) {
   const uint32_t fmt = t.is_bf16 ? 1u : 0u;
   const uint32_t idesc0 = (1u << 4) | (fmt << 7) | (fmt << 10) | ((uint32_t)(128 >> 4) << 24);
@@ -542,7 +571,8 @@ __device__ __noinline__ void mma_role_phase(const TcPlan& t, const MmaCtx c) {
   const uint32_t b_addr_base = (c.smem_b >> 4) & 0x3FFFu;
   const uint32_t a_kstep16 = (2u * t.a_plane_bytes) >> 4;
   const uint32_t a_stage16 = t.a_stage_bytes >> 4, b_stage16 = t.b_stage_bytes >> 4;
-  const int MB = t.MB, NPAD = t.NPAD, k16 = t.k16_per_ent;
+  const int MB = MB_ ? MB_ : t.MB, NPAD = t.NPAD, k16 = t.k16_per_ent;
+  const uint32_t P = (uint32_t)t.P, cout = (uint32_t)(t.NPAD >> 2), planes = (uint32_t)t.planes;
   const int nchunks = t.nchunks, ngroups = t.ngroups, num_tiles = t.num_tiles;
   const uint32_t a_stages = (uint32_t)t.a_stages, b_stages = (uint32_t)t.b_stages;
   const uint32_t A_FULL0 = c.bar0, A_EMPTY0 = c.bar0 + 8u * TC_MAX_A_STAGES, B_FULL0 = c.bar0 + 8u * (2 * TC_MAX_A_STAGES),
@@ -567,6 +597,10 @@ __device__ __noinline__ void mma_role_phase(const TcPlan& t, const MmaCtx c) {
         tc_fence_after();
         if (elect_one_sync()) {
           const uint32_t b_stage_addr = b_addr_base + sb * b_stage16;
+          if (K16 != 0) {
+            if (g == 0) issue_phase<(K16 ? K16 : 1), (MB_ ? MB_ : 1), 0, 3>(tmem_acc, a_stage_lo, b_stage_addr, a_kstep16, P, cout, planes, (uint32_t)NPAD, idesc0, ch > 0 ? 1u : 0u);
+            else issue_phase<(K16 ? K16 : 1), (MB_ ? MB_ : 1), 3, 11>(tmem_acc, a_stage_lo, b_stage_addr, a_kstep16, P, cout, planes, (uint32_t)NPAD, idesc0, 1u);
+          } else {
           const int e1 = g == 0 ? gfirst[1] : gfirst[2];
           for (int e = (g == 0 ? gfirst[0] : gfirst[1]); e < e1; ++e) {
             const uint32_t info = ent_info[e];
@@ -581,6 +615,7 @@ __device__ __noinline__ void mma_role_phase(const TcPlan& t, const MmaCtx c) {
                 umma_f16(tmem_acc + (uint32_t)(mb * NPAD) + col, ((uint64_t)DESC_HI << 32) | (a_lo + (uint32_t)j * a_kstep16 + (uint32_t)mb * 128u), bdesc,
                          idesc, (j > 0) ? 1u : acc);
             }
+          }
           }
           umma_commit(B_EMPTY0 + 8u * sb);
         }
@@ -666,7 +701,11 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
     if (t.phase_mode && lane < 16) ent_tab[32 + lane] = t.ent_info[lane];
     __syncwarp();
     const MmaCtx mc = {smem_u32(smem_a), smem_u32(smem_b), bar0, tmem_base, ent_tab, err, args.prof, first_tile, tile_step};
-    if (t.phase_mode) mma_role_phase(t, mc);
+    if (t.phase_mode) {
+      if (t.k16_per_ent == 2 && t.MB == 1) mma_role_phase<2, 1>(t, mc);
+      else if (t.k16_per_ent == 2 && t.MB == 2) mma_role_phase<2, 2>(t, mc);
+      else mma_role_phase<0, 0>(t, mc);
+    }
     else if (t.nterms == 1 && t.k16_per_ent == 2 && t.MB == 2) mma_role<2, 2>(t, mc);
     else if (t.nterms == 1 && t.k16_per_ent == 2 && t.MB == 4) mma_role<2, 4>(t, mc);
     else if (t.nterms == 1 && t.k16_per_ent == 2 && t.MB == 8) mma_role<2, 8>(t, mc);
