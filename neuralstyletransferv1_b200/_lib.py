@@ -10,7 +10,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libb200nst.so")
+LIB_PATH = os.environ.get("NST_LIB_PATH") or os.path.join(_HERE, "libb200nst.so")   # override: A/B builds (tools/ab.sh)
 
 NST_OK = 0
 ARCH = {"johnson": 0, "nst": 1, "reconet": 2}
