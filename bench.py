@@ -55,6 +55,15 @@ def peaks():
     return {"tflops": 1400.0, "hbm": 6650.0, "src": "fallback"}
 
 
+def traffic_from_profile():
+    """dram bytes (read + write) per launch of the dominant kernel from the committed `ncu --set full` summary, or None."""
+    path = os.path.join(ROOT, "profiles", "traffic.json")
+    try:
+        return json.load(open(path)).get("res_conv_dram_bytes_per_launch")
+    except Exception:
+        return None
+
+
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md)."""
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
@@ -255,7 +264,7 @@ def run_b200(args):
                "gbs": round(d["bytes"] * nprof / (d["ms"] / 1000.0) / 1e9, 1)} for d in prof]
     roofline = {"bound": "tensor", "kernel": "conv_tc_kernel (tcgen05 implicit GEMM), residual 128->128 3x3 launches",
                 "achieved": round(achieved, 2), "peak": pk["tflops"], "peak_source": pk["src"] + " bf16 dense sustained (cuBLAS)",
-                "unit": "TFLOP/s", "frac": round(achieved / pk["tflops"], 4), "traffic": None,
+                "unit": "TFLOP/s", "frac": round(achieved / pk["tflops"], 4), "traffic": traffic_from_profile(),
                 "share_of_step": round(dom_ms / total_ms, 3), "launch_ms_avg": round(dom_ms / len(dom), 4),
                 "whole_net_tflops": round(net_tflops, 2), "whole_net_frac": round(net_tflops / pk["tflops"], 4)}
 
@@ -270,7 +279,7 @@ def run_b200(args):
         "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f16" if args.precision.startswith("f16") else args.precision, "data": "synthetic",
         "config": {"workload": f"TransformerNet({args.arch}) batch {F} x {H}x{W} uint8 frames per GPU, synthetic seeded weights "
-                               f"(BASELINE configs[1]); precision={args.precision}, fp32 accumulate + fp32 activations",
+                               f"(BASELINE configs[1]); precision={args.precision}: fp16 tcgen05 operands and fp16 NHWC activation storage, fp32 accumulate and statistics",
                    "frames_per_step_per_gpu": F, "l2": "inputs larger than L2 (batch = %.0f MB uint8, activations ~660 MB/frame)" % (F * H * W * 3 / 1e6),
                    "parallelism": f"frame-batch sharding over {world} GPU(s), no collective"},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": F * H * W * 3, "d2h_bytes_per_step": F * H * W * 3},

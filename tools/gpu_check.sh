@@ -5,8 +5,8 @@ mkdir -p gpurun_out
 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?" | tee -a gpurun_out/pytest_gpu.log
 tail -3 gpurun_out/pytest_gpu.log
 python bench.py --steps 3 --warmup 3 > gpurun_out/bench.json 2> gpurun_out/bench.err; echo "bench rc=$?"
-cat gpurun_out/bench.json | cut -c1-1500
-python tools/tcprof.py johnson 8 > gpurun_out/tcprof.log 2>&1; tail -20 gpurun_out/tcprof.log
+cat gpurun_out/bench.json | cut -c1-1800
+NST_TC_PROF=1 python tools/tcprof.py johnson 8 > gpurun_out/tcprof.log 2>&1; tail -16 gpurun_out/tcprof.log
 PROF="python bench.py --frames 8 --steps 1 --warmup 3 --no-cpu-baseline"
 $PROF > gpurun_out/plain.log 2>&1 && \
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches.csv $PROF > gpurun_out/ncu1.log 2>&1
