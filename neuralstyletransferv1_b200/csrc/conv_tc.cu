@@ -712,6 +712,8 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
     else if (t.nterms == 1 && t.k16_per_ent == 2 && t.MB == 1) mma_role<2, 1>(t, mc);
     else if (t.nterms == 1 && t.k16_per_ent == 1 && t.MB == 8) mma_role<1, 8>(t, mc);
     else if (t.nterms == 1 && t.k16_per_ent == 1 && t.MB == 4) mma_role<1, 4>(t, mc);
+    else if (t.nterms == 1 && t.k16_per_ent == 1 && t.MB == 2) mma_role<1, 2>(t, mc);
+    else if (t.nterms == 1 && t.k16_per_ent == 1 && t.MB == 1) mma_role<1, 1>(t, mc);
     else mma_role<0, 0>(t, mc);
   } else if (warp < TC_FIRST_PROD_WARP) {
     // =========================== epilogue ===========================

@@ -300,7 +300,8 @@ static void tc_plan_static(const LayerSpec& s, int precision, TcPlan& t) {
   t.b_stage_bytes = t.b_term_bytes * (uint32_t)t.b_tplanes;
   t.b_stages = t.b_stage_bytes <= 8192 ? 6 : (t.b_stage_bytes <= 16384 ? 4 : 3);
   int mb = 256 / t.NPAD;                  // two accumulator buffers of MB*NPAD columns in 512
-  t.MB = std::max(1, std::min(mb, 8));
+  mb = mb >= 8 ? 8 : (mb >= 4 ? 4 : (mb >= 2 ? 2 : 1));   // powers of two: the MMA issuer is instantiated for MB = 1, 2, 4, 8
+  t.MB = mb;
 }
 
 // Shape-dependent part: tile extent, halo buffer, shared-memory budget.
