@@ -348,7 +348,7 @@ __device__ void produce_act16(const ConvParams& p, const TcPlan& t, uint8_t* sme
   const int tbl_stride = (t.NPOS + 3) & ~3;
   const int nB = (nitems + PU * TC_PROD_THREADS - 1) / (PU * TC_PROD_THREADS);     // batches per chunk
   const int is_bf16 = t.is_bf16;
-  const float lo1 = p.pre_relu ? 0.f : -INFINITY;
+  const float lo1 = (p.pre_relu || (!HAS_RESID && p.post_relu)) ? 0.f : -INFINITY;   // without a residual add the two ReLUs coincide
   const float lo2 = p.post_relu ? 0.f : -INFINITY;
   __half* side = (__half*)p.side_out;
 
@@ -397,39 +397,44 @@ __device__ void produce_act16(const ConvParams& p, const TcPlan& t, uint8_t* sme
       plane_hi = smem_a + (size_t)sa * t.a_stage_bytes + (size_t)g * t.a_plane_bytes;
     }
     const int c0 = c.ch * t.CK + g * 8;
+    // straight-line over the PU slots (no per-slot branches, so the PU dependency chains interleave): slots with nothing to do
+    // (e == -2) or structural zeros (e == -1) run on zero data and are masked at the store
+    uint32_t hi[PU][4];
+#pragma unroll
+    for (int u = 0; u < PU; ++u) {
+      const uint32_t aw[4] = {B.a[u].x, B.a[u].y, B.a[u].z, B.a[u].w};
+      uint32_t rw[4] = {0u, 0u, 0u, 0u};
+      if (HAS_RESID) { rw[0] = B.r[u].x; rw[1] = B.r[u].y; rw[2] = B.r[u].z; rw[3] = B.r[u].w; }
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const float2 av = unpack2(aw[i], 0);
+        float v0 = fmaxf(fmaf(av.x, sc[2 * i], sh[2 * i]), lo1);
+        float v1 = fmaxf(fmaf(av.y, sc[2 * i + 1], sh[2 * i + 1]), lo1);
+        if (HAS_RESID) { const float2 rv = unpack2(rw[i], 0); v0 = fmaxf(v0 + rv.x, lo2); v1 = fmaxf(v1 + rv.y, lo2); }
+        hi[u][i] = B.ent[u] >= 0 ? pack2(v0, v1, is_bf16) : 0u;
+      }
+    }
 #pragma unroll
     for (int u = 0; u < PU; ++u) {
       const int e = B.ent[u];
-      if (e == -2) continue;
       const int q = (ptid + (c.b * PU + u) * TC_PROD_THREADS) >> pshift;
-      uint32_t hi[4] = {0u, 0u, 0u, 0u};
-      if (e >= 0) {
-        const uint32_t aw[4] = {B.a[u].x, B.a[u].y, B.a[u].z, B.a[u].w};
-        uint32_t rw[4] = {0u, 0u, 0u, 0u};
-        if (HAS_RESID) { rw[0] = B.r[u].x; rw[1] = B.r[u].y; rw[2] = B.r[u].z; rw[3] = B.r[u].w; }
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-          const float2 av = unpack2(aw[i], 0);
-          float v0 = fmaxf(fmaf(av.x, sc[2 * i], sh[2 * i]), lo1);
-          float v1 = fmaxf(fmaf(av.y, sc[2 * i + 1], sh[2 * i + 1]), lo1);
-          if (HAS_RESID) { const float2 rv = unpack2(rw[i], 0); v0 += rv.x; v1 += rv.y; }
-          v0 = fmaxf(v0, lo2); v1 = fmaxf(v1, lo2);
-          hi[i] = pack2(v0, v1, is_bf16);
-        }
-        if ((e & SIDE_BIT) && !(t.dbg & 4096)) {
+      if (HAS_RESID) {
+        if (e >= 0 && (e & SIDE_BIT)) {
           // the materialised block input is stored as fp16 -- the same rounding the MMA operand gets
           uint32_t sv[4];
-          if (is_bf16) {
 #pragma unroll
-            for (int i = 0; i < 4; ++i) { const float2 f = unpack2(hi[i], 1); sv[i] = pack2(f.x, f.y, 0); }
-          } else {
+          for (int i = 0; i < 4; ++i) { if (is_bf16) { const float2 f = unpack2(hi[u][i], 1); sv[i] = pack2(f.x, f.y, 0); } else sv[i] = hi[u][i]; }
+          *reinterpret_cast<uint4*>(side + (size_t)(e & (SIDE_BIT - 1)) * p.Cin + c0) = make_uint4(sv[0], sv[1], sv[2], sv[3]);
+        }
+      } else if (side != nullptr) {
+        if (e >= 0 && (e & SIDE_BIT)) {
+          uint32_t sv[4];
 #pragma unroll
-            for (int i = 0; i < 4; ++i) sv[i] = hi[i];
-          }
+          for (int i = 0; i < 4; ++i) { if (is_bf16) { const float2 f = unpack2(hi[u][i], 1); sv[i] = pack2(f.x, f.y, 0); } else sv[i] = hi[u][i]; }
           *reinterpret_cast<uint4*>(side + (size_t)(e & (SIDE_BIT - 1)) * p.Cin + c0) = make_uint4(sv[0], sv[1], sv[2], sv[3]);
         }
       }
-      if (!(t.dbg & 2048)) *reinterpret_cast<uint4*>(plane_hi + (size_t)q * 16) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+      if (e != -2) *reinterpret_cast<uint4*>(plane_hi + (size_t)q * 16) = make_uint4(hi[u][0], hi[u][1], hi[u][2], hi[u][3]);
     }
     if (c.b == nB - 1) {
       fence_proxy_async_smem();
