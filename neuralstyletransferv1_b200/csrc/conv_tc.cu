@@ -498,6 +498,7 @@ __device__ __noinline__ void mma_role(const TcPlan& t, const MmaCtx c) {
   const uint32_t a_term16 = t.a_term_bytes >> 4, b_term16 = t.b_term_bytes >> 4, b_ent16 = t.b_ent_bytes >> 4;
   const int MB = MB_ ? MB_ : t.MB, NPAD = t.NPAD, k16 = t.k16_per_ent, nterms = t.nterms, tg = t.tg, nent = t.nent;
   const int nchunks = t.nchunks, ngroups = t.ngroups, num_tiles = t.num_tiles, dbg = t.dbg;
+  const bool resident = t.b_resident != 0;
   const uint32_t a_stages = (uint32_t)t.a_stages, b_stages = (uint32_t)t.b_stages;
   const uint32_t A_FULL0 = c.bar0, A_EMPTY0 = c.bar0 + 8u * TC_MAX_A_STAGES, B_FULL0 = c.bar0 + 8u * (2 * TC_MAX_A_STAGES),
                  B_EMPTY0 = B_FULL0 + 8u * TC_MAX_B_STAGES, ACC_FULL0 = B_FULL0 + 8u * (2 * TC_MAX_B_STAGES), ACC_EMPTY0 = ACC_FULL0 + 16u;
@@ -515,14 +516,14 @@ __device__ __noinline__ void mma_role(const TcPlan& t, const MmaCtx c) {
       const uint32_t a_stage_lo = a_lo_base + sa * a_stage16;
       int ent = 0;
       for (int g = 0; g < ngroups; ++g) {
-        if (!(dbg & 64)) mbar_wait(B_FULL0 + 8u * sb, pb, c.err, 4, wprof);
+        if (!(dbg & 64)) mbar_wait(B_FULL0 + 8u * sb, resident ? 0u : pb, c.err, 4, wprof);
         tc_fence_after();
         if (elect_one_sync()) {
           const IssueArgs ia = {tmem_acc, a_stage_lo, b_lo_base + sb * b_stage16, b_ent16, a_kstep16, b_kstep16, a_term16, b_term16, (uint32_t)NPAD, idesc,
                                 c.ent_tab + ent, min(tg, nent - ent), acc_on};
           if (K16 != 0) issue_group<(K16 ? K16 : 1), (MB_ ? MB_ : 1)>(ia);
           else issue_group_generic(ia, k16, MB, nterms);
-          umma_commit(B_EMPTY0 + 8u * sb);
+          if (!resident) umma_commit(B_EMPTY0 + 8u * sb);
         }
         __syncwarp();
         acc_on = 1u;
@@ -688,6 +689,12 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
       uint32_t sb = 0, pb = 0;
       const uint8_t* wp = reinterpret_cast<const uint8_t*>(args.wpack);
       const int nstage_per_tile = t.nchunks * t.ngroups;
+      if (t.b_resident) {
+        for (int g = 0; g < nstage_per_tile; ++g) {
+          mbar_arrive_expect_tx(B_FULL(g), t.b_stage_bytes);
+          bulk_g2s(smem_u32(smem_b + (size_t)g * t.b_stage_bytes), wp + (size_t)g * t.b_stage_bytes, t.b_stage_bytes, B_FULL(g));
+        }
+      } else
       for (int tile = first_tile; tile < t.num_tiles; tile += tile_step) {
         for (int g = 0; g < nstage_per_tile; ++g) {
           mbar_wait(B_EMPTY(sb), pb ^ 1u, err, 1, wprof);

@@ -35,6 +35,7 @@ struct TcPlan {
   int NPAD;                 // UMMA N (Cout padded to a multiple of 16)
   int tg, ngroups;          // entries per weight stage, stages per chunk
   int a_stages, b_stages;
+  int b_resident;           // the layer's whole weight set fits the B ring: load every stage once, never recycle
   int nterms;               // 1, or 3 (hi*hi + lo*hi + hi*lo)
   int a_tplanes, b_tplanes; // operand planes kept (1, or 2 = hi and lo)
   int is_bf16;

@@ -299,23 +299,84 @@ static void tc_plan_static(const LayerSpec& s, int precision, TcPlan& t) {
   t.b_term_bytes = (uint32_t)tg * t.b_ent_bytes;
   t.b_stage_bytes = t.b_term_bytes * (uint32_t)t.b_tplanes;
   t.b_stages = t.b_stage_bytes <= 8192 ? 6 : (t.b_stage_bytes <= 16384 ? 4 : 3);
+  if (t.fold_s && t.nchunks * t.ngroups <= TC_MAX_B_STAGES && (size_t)t.nchunks * t.ngroups * t.b_stage_bytes <= 32768) {
+    t.b_resident = 1;                    // 18-27 KB of weights stay in shared memory for the whole launch: room for larger tiles
+    t.b_stages = t.nchunks * t.ngroups;
+  }
   int mb = 256 / t.NPAD;                  // two accumulator buffers of MB*NPAD columns in 512
   mb = mb >= 8 ? 8 : (mb >= 4 ? 4 : (mb >= 2 ? 2 : 1));   // powers of two: the MMA issuer is instantiated for MB = 1, 2, 4, 8
   t.MB = mb;
 }
 
 // Shape-dependent part: tile extent, halo buffer, shared-memory budget.
+// Lay out one candidate tile (TH x TW outputs, halo pitch P, MB M-blocks) in shared memory; false if it does not fit.
+static bool tc_layout(const ConvParams& p, TcPlan& t, int MB, int bTH, int bTW, int bP) {
+  const int e = p.ks - 1;
+  t.TH = bTH; t.TW = bTW; t.P = bP;
+  const int Mused = ceil_div(bTH * bP, 128);
+  const int MBu = std::min(MB, std::max(1, Mused));
+  int max_off = 0;
+  if (p.stride == 1) {
+    t.halo_h = bTH + e; t.halo_w = bP; t.SUBPOS = 0;
+    int k = 0;
+    if (t.pair_mode) {
+      for (int r = 0; r < p.ks; ++r) for (int sp = 0; sp < (p.ks + 1) / 2; ++sp) t.ent_off[k++] = r * bP + 2 * sp;
+      max_off = e * bP + e + 1;
+    } else {
+      if (t.phase_mode) { for (int i = 0; i < PH_NENT; ++i) t.ent_off[k++] = PH_R[i] * bP + PH_S[i]; max_off = e * bP + e; }
+      else if (t.fold_s) { for (int r = 0; r < p.ks; ++r) t.ent_off[k++] = r * bP; max_off = e * bP; }
+      else { for (int r = 0; r < p.ks; ++r) for (int s = 0; s < p.ks; ++s) t.ent_off[k++] = r * bP + s; max_off = e * bP + e; }
+    }
+    t.NPOS = std::max(MBu * 128 + max_off + 2, t.halo_h * bP + 2);
+  } else {
+    t.halo_h = 2 * bTH + 1; t.halo_w = 2 * bTW + 1;
+    t.SUBPOS = (bTH + 1) * bP + 2;
+    int k = 0;
+    for (int r = 0; r < 3; ++r) for (int s = 0; s < 3; ++s) t.ent_off[k++] = ((r & 1) * 2 + (s & 1)) * t.SUBPOS + (r >> 1) * bP + (s >> 1);
+    max_off = 3 * t.SUBPOS + bP + 1;
+    t.NPOS = std::max(MBu * 128 + max_off + 2, 4 * t.SUBPOS);
+  }
+  // plane stride (in 16-byte units) chosen so the producers' 8-lane store phases cover all banks
+  if (t.planes == 4) { while (t.NPOS % 8 != 2) ++t.NPOS; }
+  else if (t.planes == 2) { while (t.NPOS % 8 != 4) ++t.NPOS; }
+  else { t.NPOS = (int)round_up((size_t)t.NPOS, 2); }
+  t.a_plane_bytes = (uint32_t)t.NPOS * 16u;
+  t.a_term_bytes = t.a_plane_bytes * (uint32_t)t.planes;
+  t.a_stage_bytes = (uint32_t)round_up((size_t)t.a_term_bytes * t.a_tplanes, 128);
+  if (t.a_plane_bytes >= (1u << 18)) return false;
+  const int b_total = t.b_stages * (int)t.b_stage_bytes;
+  // barriers + TMEM slot + two per-tile source tables [NPOS] (current / next tile) + per-sample norm coefficients [Cin<=256]
+  // + epilogue scratch: fold ring, or per-warp channel statistics
+  const int bar_bytes = 640 + 2 * (int)round_up((size_t)t.NPOS * 4, 16) + 256 * 8 + (t.fold_s ? TC_FOLD_RING_BYTES : 4 * t.NPAD * 8);
+  const int avail = TC_SMEM_LIMIT - b_total - bar_bytes;
+  const int a_stages = avail / (int)t.a_stage_bytes;
+  const int want = t.nchunks == 1 ? 2 : 3;
+  if (a_stages < 2 && MB > 1) return false;
+  if (a_stages < 1) return false;
+  t.a_stages = std::min(a_stages, std::min(TC_MAX_A_STAGES, want + 1));
+  t.MB = MBu;
+  t.tiles_x = ceil_div(p.Wo, t.TW);
+  t.tiles_y = ceil_div(p.Ho, t.TH);
+  t.num_tiles = t.tiles_x * t.tiles_y * p.N;
+  t.smem_bytes = (uint32_t)(t.a_stages * t.a_stage_bytes + b_total + bar_bytes);
+  return true;
+}
+
+// Shape-dependent part: tile extent, halo buffer, shared-memory budget.  Every (MB, TH) candidate is laid out and costed;
+// the model is the measured one: an MMA costs its table value, an operand-producer item ~3.4 SM cycles, and the two overlap.
 static bool tc_plan_geometry(const ConvParams& p, TcPlan& t) {
   if ((long long)p.N * p.Hs * p.Ws >= (1ll << 30)) return false;   // source-table entries are 30-bit pixel indices
   const int e = p.ks - 1;
-  for (int MB = t.MB; MB >= 1; MB = (MB > 1 ? MB / 2 : 0)) {
+  const TcPlan base = t;
+  double best = 1e30;
+  TcPlan best_plan = t;
+  bool found = false;
+  // measured tcgen05.mma cost (tools/umma_bench.cu): N=16 39, N=32 40, N=64 48, N=128 64, N=256 128 cycles
+  const double mma_one = t.NPAD >= 128 ? t.NPAD / 2.0 : 32.0 + t.NPAD / 4.0;
+  for (int MB = base.MB; MB >= 1; MB /= 2) {
     const int M = MB * 128;
-    // measured tcgen05.mma cost (tools/umma_bench.cu): N=16 39, N=32 40, N=64 48, N=128 64, N=256 128 cycles
-    const double mma_one = t.NPAD >= 128 ? t.NPAD / 2.0 : 32.0 + t.NPAD / 4.0;
     double mma_cyc = (double)MB * t.nchunks * t.nent * t.k16_per_ent * t.nterms * mma_one;
     if (t.phase_mode) mma_cyc = (double)MB * t.nchunks * t.k16_per_ent * (t.NPAD * 2.5);
-    double best = 1e30;
-    int bTH = 0, bTW = 0, bP = 0;
     for (int TH = 1; TH <= std::min(64, M); ++TH) {
       int P = M / TH;
       int TW = p.stride == 1 ? P - e : P - 1;
@@ -323,62 +384,17 @@ static bool tc_plan_geometry(const ConvParams& p, TcPlan& t) {
       if (TW > p.Wo) { TW = p.Wo; P = p.stride == 1 ? TW + e : TW + 1; }
       if (TW < 4 && p.Wo >= 4) continue;
       const int THe = std::min(TH, p.Ho);
-      const double tiles = (double)ceil_div(p.Ho, THe) * ceil_div(p.Wo, TW);
-      const double halo = p.stride == 1 ? (double)(THe + e) * P : 4.0 * (THe + 1) * P;
-      const double prod_cyc = halo * t.planes * t.nchunks * 10.0;
-      const double cost = tiles * (std::max(mma_cyc, prod_cyc) + 0.15 * std::min(mma_cyc, prod_cyc) + 2000.0);
-      if (cost < best) { best = cost; bTH = THe; bTW = TW; bP = P; }
+      TcPlan cand = base;
+      if (!tc_layout(p, cand, MB, THe, TW, P)) continue;
+      const double tiles = (double)cand.tiles_x * cand.tiles_y;
+      const double prod_cyc = (double)cand.NPOS * cand.planes * cand.nchunks * 3.4;
+      const double cost = tiles * (std::max(mma_cyc, prod_cyc) + 0.25 * std::min(mma_cyc, prod_cyc) + 1500.0);
+      if (cost < best) { best = cost; best_plan = cand; found = true; }
     }
-    if (bTH == 0) continue;
-    t.TH = bTH; t.TW = bTW; t.P = bP;
-    const int Mused = ceil_div(bTH * bP, 128);
-    const int MBu = std::min(MB, std::max(1, Mused));
-    int max_off = 0;
-    if (p.stride == 1) {
-      t.halo_h = bTH + e; t.halo_w = bP; t.SUBPOS = 0;
-      int k = 0;
-      if (t.pair_mode) {
-        for (int r = 0; r < p.ks; ++r) for (int sp = 0; sp < (p.ks + 1) / 2; ++sp) t.ent_off[k++] = r * bP + 2 * sp;
-        max_off = e * bP + e + 1;
-      } else {
-        if (t.phase_mode) { for (int i = 0; i < PH_NENT; ++i) t.ent_off[k++] = PH_R[i] * bP + PH_S[i]; max_off = e * bP + e; }
-        else if (t.fold_s) { for (int r = 0; r < p.ks; ++r) t.ent_off[k++] = r * bP; max_off = e * bP; }
-        else { for (int r = 0; r < p.ks; ++r) for (int s = 0; s < p.ks; ++s) t.ent_off[k++] = r * bP + s; max_off = e * bP + e; }
-      }
-      t.NPOS = std::max(MBu * 128 + max_off + 2, t.halo_h * bP + 2);
-    } else {
-      t.halo_h = 2 * bTH + 1; t.halo_w = 2 * bTW + 1;
-      t.SUBPOS = (bTH + 1) * bP + 2;
-      int k = 0;
-      for (int r = 0; r < 3; ++r) for (int s = 0; s < 3; ++s) t.ent_off[k++] = ((r & 1) * 2 + (s & 1)) * t.SUBPOS + (r >> 1) * bP + (s >> 1);
-      max_off = 3 * t.SUBPOS + bP + 1;
-      t.NPOS = std::max(MBu * 128 + max_off + 2, 4 * t.SUBPOS);
-    }
-    // plane stride (in 16-byte units) chosen so the producers' 8-lane store phases cover all banks
-    if (t.planes == 4) { while (t.NPOS % 8 != 2) ++t.NPOS; }
-    else if (t.planes == 2) { while (t.NPOS % 8 != 4) ++t.NPOS; }
-    else { t.NPOS = (int)round_up((size_t)t.NPOS, 2); }
-    t.a_plane_bytes = (uint32_t)t.NPOS * 16u;
-    t.a_term_bytes = t.a_plane_bytes * (uint32_t)t.planes;
-    t.a_stage_bytes = (uint32_t)round_up((size_t)t.a_term_bytes * t.a_tplanes, 128);
-    const int b_total = t.b_stages * (int)t.b_stage_bytes;
-    // barriers + TMEM slot + two per-tile source tables [NPOS] (current / next tile) + per-sample norm coefficients [Cin<=256]
-    const int bar_bytes = 640 + 2 * (int)round_up((size_t)t.NPOS * 4, 16) + 256 * 8 + (t.fold_s ? TC_FOLD_RING_BYTES : 4 * t.NPAD * 8);   // + epilogue scratch: fold ring, or per-warp channel statistics
-    const int avail = TC_SMEM_LIMIT - b_total - bar_bytes;
-    int a_stages = avail / (int)t.a_stage_bytes;
-    const int want = t.nchunks == 1 ? 2 : 3;
-    if (a_stages < 2 && MB > 1) continue;        // try a smaller tile
-    if (a_stages < 1) return false;
-    t.a_stages = std::min(a_stages, std::min(TC_MAX_A_STAGES, want + 1));
-    t.MB = MBu;
-    t.tiles_x = ceil_div(p.Wo, t.TW);
-    t.tiles_y = ceil_div(p.Ho, t.TH);
-    t.num_tiles = t.tiles_x * t.tiles_y * p.N;
-    t.smem_bytes = (uint32_t)(t.a_stages * t.a_stage_bytes + b_total + bar_bytes);
-    if (t.a_plane_bytes >= (1u << 18)) return false;
-    return true;
   }
-  return false;
+  if (!found) return false;
+  t = best_plan;
+  return true;
 }
 
 // Host packing of one layer's weights into the weight-stage images the kernel bulk-copies:
