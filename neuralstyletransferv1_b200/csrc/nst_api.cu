@@ -364,7 +364,7 @@ static bool tc_layout(const ConvParams& p, TcPlan& t, int MB, int bTH, int bTW, 
 
 // Shape-dependent part: tile extent, halo buffer, shared-memory budget.  Every (MB, TH) candidate is laid out and costed;
 // the model is the measured one: an MMA costs its table value, an operand-producer item ~3.4 SM cycles, and the two overlap.
-static bool tc_plan_geometry(const ConvParams& p, TcPlan& t) {
+static bool tc_plan_geometry(const ConvParams& p, TcPlan& t, int force_TH = 0, int force_MB = 0) {
   if ((long long)p.N * p.Hs * p.Ws >= (1ll << 30)) return false;   // source-table entries are 30-bit pixel indices
   const int e = p.ks - 1;
   const TcPlan base = t;
@@ -374,10 +374,12 @@ static bool tc_plan_geometry(const ConvParams& p, TcPlan& t) {
   // measured tcgen05.mma cost (tools/umma_bench.cu): N=16 39, N=32 40, N=64 48, N=128 64, N=256 128 cycles
   const double mma_one = t.NPAD >= 128 ? t.NPAD / 2.0 : 32.0 + t.NPAD / 4.0;
   for (int MB = base.MB; MB >= 1; MB /= 2) {
+    if (force_MB && MB != force_MB) continue;
     const int M = MB * 128;
     double mma_cyc = (double)MB * t.nchunks * t.nent * t.k16_per_ent * t.nterms * mma_one;
     if (t.phase_mode) mma_cyc = (double)MB * t.nchunks * t.k16_per_ent * (t.NPAD * 2.5);
     for (int TH = 1; TH <= std::min(64, M); ++TH) {
+      if (force_TH && TH != force_TH) continue;
       int P = M / TH;
       int TW = p.stride == 1 ? P - e : P - 1;
       if (TW < 1) continue;
@@ -387,7 +389,9 @@ static bool tc_plan_geometry(const ConvParams& p, TcPlan& t) {
       TcPlan cand = base;
       if (!tc_layout(p, cand, MB, THe, TW, P)) continue;
       const double tiles = (double)cand.tiles_x * cand.tiles_y;
-      const double prod_cyc = (double)cand.NPOS * cand.planes * cand.nchunks * 3.4;
+      // short halo rows gather worse (tools/tile_sweep.py: wide, flat tiles win by 3-7 % at equal position count)
+      const double row_factor = p.stride == 1 ? 1.0 + 8.0 / cand.P : 1.0;
+      const double prod_cyc = (double)cand.NPOS * cand.planes * cand.nchunks * 3.4 * row_factor;
       const double cost = tiles * (std::max(mma_cyc, prod_cyc) + 0.25 * std::min(mma_cyc, prod_cyc) + 1500.0);
       if (cost < best) { best = cost; best_plan = cand; found = true; }
     }
@@ -686,6 +690,14 @@ static int make_plan(nst_handle* h, int N, int H, int W) {
       lp.bytes = in_b + out_b + esz * (double)p.Hs * p.Ws * s.cin * ((s.resid >= 0 ? 1 : 0) + (s.side >= 0 ? 1 : 0));
     }
     lp.use_tc = h->dev[li].tc_ok && ((h->tc_layer_mask >> li) & 1ull);
+    int fTH = 0, fMB = 0;
+    if (const char* f = getenv("NST_TC_FORCE")) {      // tuning aid: "layer:TH:MB;layer:TH:MB" restricts the tile search (tools/tile_sweep.py)
+      for (const char* q = f; q && *q; ) {
+        int l = -1, th = 0, mb = 0;
+        if (sscanf(q, "%d:%d:%d", &l, &th, &mb) == 3 && l == (int)li) { fTH = th; fMB = mb; }
+        q = strchr(q, ';'); if (q) ++q;
+      }
+    }
     if (lp.use_tc) {
       lp.t = h->dev[li].tc_static;
       if (lp.t.phase_mode) {
@@ -693,8 +705,8 @@ static int make_plan(nst_handle* h, int N, int H, int W) {
         ConvParams q = p;
         q.phase_mode = 1; q.map_mode = MAP_IDENTITY; q.pad_mode = PAD_REPLICATE;
         q.Hc = p.Hs; q.Wc = p.Ws; q.Ho = p.Hs; q.Wo = p.Ws;
-        if (tc_plan_geometry(q, lp.t)) p = q; else lp.use_tc = false;
-      } else if (!tc_plan_geometry(p, lp.t)) lp.use_tc = false;
+        if (tc_plan_geometry(q, lp.t, fTH, fMB)) p = q; else lp.use_tc = false;
+      } else if (!tc_plan_geometry(p, lp.t, fTH, fMB)) lp.use_tc = false;
     }
   }
   size_t off = 0;
