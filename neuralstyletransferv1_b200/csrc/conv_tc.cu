@@ -543,13 +543,14 @@ __device__ __noinline__ void mma_role(const TcPlan& t, const MmaCtx c) {
 // Sub-pixel (phase) layers: every entry multiplies its own accumulator column range [col, col+n) with its own N.
 // The entry table is compile-time (it mirrors PH_* in nst_api.cu), so a weight stage unrolls into straight-line
 // uniform-register code; a runtime-table loop cost ~290 cycles per MMA (descriptors built in vector registers).
-template <int K16, int MB, int E0, int E1>
+template <int KIND, int K16, int MB, int E0, int E1>
 __device__ __forceinline__ void issue_phase(uint32_t tmem_acc, uint32_t a_stage_lo, uint32_t b_stage_addr, uint32_t a_kstep16, uint32_t P,
                                             uint32_t cout, uint32_t planes, uint32_t npad, uint32_t idesc0, uint32_t acc_first) {
-  constexpr int R[11]  = {1, 0, 2, 1, 1, 1, 1, 0, 0, 2, 2};
-  constexpr int S[11]  = {1, 1, 1, 0, 0, 2, 2, 0, 2, 0, 2};
-  constexpr int P0[11] = {0, 0, 2, 0, 2, 1, 3, 0, 1, 2, 3};
-  constexpr int NP[11] = {4, 2, 2, 1, 1, 1, 1, 1, 1, 1, 1};
+  // KIND 1: upsample + reflect pad + conv3 (11 entries); KIND 2: ConvTranspose2d k3 s2 p1 op1 (5 entries)
+  constexpr int R[11]  = {1, KIND == 1 ? 0 : 2, KIND == 1 ? 2 : 1, 1, KIND == 1 ? 1 : 2, 1, 1, 0, 0, 2, 2};
+  constexpr int S[11]  = {1, 1, KIND == 1 ? 1 : 2, KIND == 1 ? 0 : 2, KIND == 1 ? 0 : 2, 2, 2, 0, 2, 0, 2};
+  constexpr int P0[11] = {0, KIND == 1 ? 0 : 2, KIND == 1 ? 2 : 1, KIND == 1 ? 0 : 3, KIND == 1 ? 2 : 3, 1, 3, 0, 1, 2, 3};
+  constexpr int NP[11] = {4, 2, KIND == 1 ? 2 : 1, 1, 1, 1, 1, 1, 1, 1, 1};
   uint32_t units = 0;
 #pragma unroll
   for (int e = E0; e < E1; ++e) {
@@ -569,7 +570,7 @@ __device__ __forceinline__ void issue_phase(uint32_t tmem_acc, uint32_t a_stage_
   }
 }
 
-template <int K16, int MB_>
+template <int KIND, int K16, int MB_>
 __device__ __noinline__ void mma_role_phase(const TcPlan& t, const MmaCtx c) {
   const uint32_t fmt = t.is_bf16 ? 1u : 0u;
   const uint32_t idesc0 = (1u << 4) | (fmt << 7) | (fmt << 10) | ((uint32_t)(128 >> 4) << 24);
@@ -604,8 +605,9 @@ __device__ __noinline__ void mma_role_phase(const TcPlan& t, const MmaCtx c) {
         if (elect_one_sync()) {
           const uint32_t b_stage_addr = b_addr_base + sb * b_stage16;
           if (K16 != 0) {
-            if (g == 0) issue_phase<(K16 ? K16 : 1), (MB_ ? MB_ : 1), 0, 3>(tmem_acc, a_stage_lo, b_stage_addr, a_kstep16, P, cout, planes, (uint32_t)NPAD, idesc0, ch > 0 ? 1u : 0u);
-            else issue_phase<(K16 ? K16 : 1), (MB_ ? MB_ : 1), 3, 11>(tmem_acc, a_stage_lo, b_stage_addr, a_kstep16, P, cout, planes, (uint32_t)NPAD, idesc0, 1u);
+            constexpr int G1 = KIND == 1 ? 3 : 2, NE = KIND == 1 ? 11 : 5;
+            if (g == 0) issue_phase<KIND, (K16 ? K16 : 1), (MB_ ? MB_ : 1), 0, G1>(tmem_acc, a_stage_lo, b_stage_addr, a_kstep16, P, cout, planes, (uint32_t)NPAD, idesc0, ch > 0 ? 1u : 0u);
+            else issue_phase<KIND, (K16 ? K16 : 1), (MB_ ? MB_ : 1), G1, NE>(tmem_acc, a_stage_lo, b_stage_addr, a_kstep16, P, cout, planes, (uint32_t)NPAD, idesc0, 1u);
           } else {
           const int e1 = g == 0 ? gfirst[1] : gfirst[2];
           for (int e = (g == 0 ? gfirst[0] : gfirst[1]); e < e1; ++e) {
@@ -714,9 +716,11 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
     __syncwarp();
     const MmaCtx mc = {smem_u32(smem_a), smem_u32(smem_b), bar0, tmem_base, ent_tab, err, args.prof, first_tile, tile_step};
     if (t.phase_mode) {
-      if (t.k16_per_ent == 2 && t.MB == 1) mma_role_phase<2, 1>(t, mc);
-      else if (t.k16_per_ent == 2 && t.MB == 2) mma_role_phase<2, 2>(t, mc);
-      else mma_role_phase<0, 0>(t, mc);
+      if (t.phase_mode == 1 && t.k16_per_ent == 2 && t.MB == 1) mma_role_phase<1, 2, 1>(t, mc);
+      else if (t.phase_mode == 1 && t.k16_per_ent == 2 && t.MB == 2) mma_role_phase<1, 2, 2>(t, mc);
+      else if (t.phase_mode == 2 && t.k16_per_ent == 2 && t.MB == 1) mma_role_phase<2, 2, 1>(t, mc);
+      else if (t.phase_mode == 2 && t.k16_per_ent == 2 && t.MB == 2) mma_role_phase<2, 2, 2>(t, mc);
+      else mma_role_phase<1, 0, 0>(t, mc);
     }
     else if (t.nterms == 1 && t.k16_per_ent == 2 && t.MB == 2) mma_role<2, 2>(t, mc);
     else if (t.nterms == 1 && t.k16_per_ent == 2 && t.MB == 4) mma_role<2, 4>(t, mc);

@@ -232,35 +232,47 @@ static bool tc_supported(const LayerSpec& s) {
 // output pixel (2i+a, 2j+b) only sees the 2x2 low-res neighbourhood of (i,j), so the layer is a 3x3 conv over the LOW-RES
 // tensor with replicate padding and N = 4 phases x Cout columns, where tap (r,s) feeds only some phases.  Entry table:
 // low-res tap (r,s), first phase (= a*2+b), number of adjacent phases.  Entry 0 covers every column (it initialises the accumulator).
-static const int PH_NENT = 11;
-static const int PH_R[PH_NENT]  = {1, 0, 2, 1, 1, 1, 1, 0, 0, 2, 2};
-static const int PH_S[PH_NENT]  = {1, 1, 1, 0, 0, 2, 2, 0, 2, 0, 2};
-static const int PH_P0[PH_NENT] = {0, 0, 2, 0, 2, 1, 3, 0, 1, 2, 3};
-static const int PH_NP[PH_NENT] = {4, 2, 2, 1, 1, 1, 1, 1, 1, 1, 1};
-// original taps r' that land on low-res tap r for row/column phase a:  a=0: {0} {1,2} {};  a=1: {} {0,1} {2}
-static bool ph_hits(int a, int r, int rp) {
-  if (a == 0) return (r == 0 && rp == 0) || (r == 1 && rp >= 1);
-  return (r == 1 && rp <= 1) || (r == 2 && rp == 2);
+// kind 1 (upsample + reflect pad + conv3), kind 2 (ConvTranspose2d k3 s2 p1 op1, transformer_net_nst.py:46-59: output (2i+a, 2j+b)
+// reads low-res rows i (kernel row 1 for a=0, row 0 for a=1 of the equivalent flipped kernel) and i+1 (row 2, a=1 only), zero padded).
+static const int PH_NENT_K[3] = {0, 11, 5};
+static const int PH_G1_K[3] = {0, 3, 2};                 // entries in the first weight stage
+static const int PH_R_K[3][11]  = {{0}, {1, 0, 2, 1, 1, 1, 1, 0, 0, 2, 2}, {1, 2, 1, 1, 2}};
+static const int PH_S_K[3][11]  = {{0}, {1, 1, 1, 0, 0, 2, 2, 0, 2, 0, 2}, {1, 1, 2, 2, 2}};
+static const int PH_P0_K[3][11] = {{0}, {0, 0, 2, 0, 2, 1, 3, 0, 1, 2, 3}, {0, 2, 1, 3, 3}};
+static const int PH_NP_K[3][11] = {{0}, {4, 2, 2, 1, 1, 1, 1, 1, 1, 1, 1}, {4, 2, 1, 1, 1}};
+// original taps r' that land on low-res tap r for row/column phase a
+static bool ph_hits(int kind, int a, int r, int rp) {
+  if (kind == 1) {                                       // a=0: {0} {1,2} {};  a=1: {} {0,1} {2}
+    if (a == 0) return (r == 0 && rp == 0) || (r == 1 && rp >= 1);
+    return (r == 1 && rp <= 1) || (r == 2 && rp == 2);
+  }
+  if (a == 0) return r == 1 && rp == 1;                  // kind 2: a=0: {} {1} {};  a=1: {} {0} {2}
+  return (r == 1 && rp == 0) || (r == 2 && rp == 2);
 }
-static bool phase_eligible(const LayerSpec& s, int precision) {
-  return s.map_mode == MAP_UP2 && s.pad_mode == PAD_REFLECT && s.ks == 3 && s.stride == 1 && s.cout % 16 == 0 && 4 * s.cout <= 256 &&
-         s.cin % 16 == 0 && precision != NST_PREC_F16X3 && !getenv("NST_NO_PHASE");
+static int phase_kind(const LayerSpec& s, int precision) {
+  if (getenv("NST_NO_PHASE") || precision == NST_PREC_F16X3) return 0;
+  if (s.ks != 3 || s.stride != 1 || s.cout % 16 != 0 || 4 * s.cout > 256 || s.cin % 16 != 0) return 0;
+  if (s.map_mode == MAP_UP2 && s.pad_mode == PAD_REFLECT) return 1;
+  if (s.map_mode == MAP_ZERO_INSERT2 && s.pad_mode == PAD_ZERO) return 2;
+  return 0;
 }
 
 static void tc_plan_static(const LayerSpec& s, int precision, TcPlan& t) {
   memset(&t, 0, sizeof(t));
-  if (phase_eligible(s, precision)) {
-    t.phase_mode = 1;
+  if (const int kind = phase_kind(s, precision)) {
+    t.phase_mode = kind;
+    const int PH_NENT = PH_NENT_K[kind];
+    const int* PH_P0 = PH_P0_K[kind]; const int* PH_NP = PH_NP_K[kind];
     t.NPAD = 4 * s.cout;
     t.CK = (s.cin % 32 == 0) ? 32 : 16;
     t.planes = t.CK / 8; t.nchunks = s.cin / t.CK; t.nent = PH_NENT; t.k16_per_ent = t.CK / 16;
     t.is_bf16 = precision == NST_PREC_BF16;
     t.nterms = 1; t.a_tplanes = 1; t.b_tplanes = 1;
     t.ngroups = 2; t.tg = 8;
-    t.grp_first[0] = 0; t.grp_first[1] = 3; t.grp_first[2] = PH_NENT;
+    t.grp_first[0] = 0; t.grp_first[1] = PH_G1_K[kind]; t.grp_first[2] = PH_NENT;
     uint32_t grp_bytes[2] = {0, 0};
     for (int e = 0; e < PH_NENT; ++e) {
-      const int g = e < 3 ? 0 : 1;
+      const int g = e < PH_G1_K[kind] ? 0 : 1;
       const int n = PH_NP[e] * s.cout;
       t.ent_info[e] = (uint32_t)(PH_P0[e] * s.cout) | ((uint32_t)(n / 16) << 9) | ((grp_bytes[g] / 16u) << 14);
       grp_bytes[g] += (uint32_t)(t.planes * n * 16);
@@ -323,7 +335,7 @@ static bool tc_layout(const ConvParams& p, TcPlan& t, int MB, int bTH, int bTW, 
       for (int r = 0; r < p.ks; ++r) for (int sp = 0; sp < (p.ks + 1) / 2; ++sp) t.ent_off[k++] = r * bP + 2 * sp;
       max_off = e * bP + e + 1;
     } else {
-      if (t.phase_mode) { for (int i = 0; i < PH_NENT; ++i) t.ent_off[k++] = PH_R[i] * bP + PH_S[i]; max_off = e * bP + e; }
+      if (t.phase_mode) { for (int i = 0; i < PH_NENT_K[t.phase_mode]; ++i) t.ent_off[k++] = PH_R_K[t.phase_mode][i] * bP + PH_S_K[t.phase_mode][i]; max_off = e * bP + e; }
       else if (t.fold_s) { for (int r = 0; r < p.ks; ++r) t.ent_off[k++] = r * bP; max_off = e * bP; }
       else { for (int r = 0; r < p.ks; ++r) for (int s = 0; s < p.ks; ++s) t.ent_off[k++] = r * bP + s; max_off = e * bP + e; }
     }
@@ -377,7 +389,7 @@ static bool tc_plan_geometry(const ConvParams& p, TcPlan& t, int force_TH = 0, i
     if (force_MB && MB != force_MB) continue;
     const int M = MB * 128;
     double mma_cyc = (double)MB * t.nchunks * t.nent * t.k16_per_ent * t.nterms * mma_one;
-    if (t.phase_mode) mma_cyc = (double)MB * t.nchunks * t.k16_per_ent * (t.NPAD * 2.5);
+    if (t.phase_mode) mma_cyc = (double)MB * t.nchunks * t.k16_per_ent * (t.NPAD * (t.phase_mode == 1 ? 2.5 : 1.4));
     for (int TH = 1; TH <= std::min(64, M); ++TH) {
       if (force_TH && TH != force_TH) continue;
       int P = M / TH;
@@ -408,6 +420,8 @@ static std::vector<uint16_t> tc_pack_weights(const LayerSpec& s, const TcPlan& t
   std::vector<uint16_t> out((size_t)t.nchunks * t.ngroups * stage_elems, 0);
   if (t.phase_mode) {
     // entry e at [chunk][stage g][B offset]: [8-channel plane][n = (phase - phase0)*Cout + co][8] of the pre-summed phase weights
+    const int kind = t.phase_mode, PH_NENT = PH_NENT_K[kind];
+    const int *PH_R = PH_R_K[kind], *PH_S = PH_S_K[kind], *PH_P0 = PH_P0_K[kind], *PH_NP = PH_NP_K[kind];
     for (int ch = 0; ch < t.nchunks; ++ch) for (int e = 0; e < PH_NENT; ++e) {
       const int g = e < t.grp_first[1] ? 0 : 1;
       const int n_e = PH_NP[e] * s.cout;
@@ -417,7 +431,7 @@ static std::vector<uint16_t> tc_pack_weights(const LayerSpec& s, const TcPlan& t
         const int a = ph >> 1, b = ph & 1;
         float v = 0.f;
         for (int rp = 0; rp < 3; ++rp) for (int sp = 0; sp < 3; ++sp)
-          if (ph_hits(a, PH_R[e], rp) && ph_hits(b, PH_S[e], sp)) v += w_oihw[(((size_t)co * s.cin + ci) * 3 + rp) * 3 + sp];
+          if (ph_hits(kind, a, PH_R[e], rp) && ph_hits(kind, b, PH_S[e], sp)) v += w_oihw[(((size_t)co * s.cin + ci) * 3 + rp) * 3 + sp];
         uint16_t u;
         if (t.is_bf16) { __nv_bfloat16 hv = __float2bfloat16_rn(v); memcpy(&u, &hv, 2); } else { __half hv = __float2half_rn(v); memcpy(&u, &hv, 2); }
         out[base + ((size_t)kp * n_e + n) * 8 + i] = u;
@@ -703,7 +717,7 @@ static int make_plan(nst_handle* h, int N, int H, int W) {
       if (lp.t.phase_mode) {
         // tile over the low-res grid; the epilogue scatters the four phases into the [N, 2Hs, 2Ws, Cout] output
         ConvParams q = p;
-        q.phase_mode = 1; q.map_mode = MAP_IDENTITY; q.pad_mode = PAD_REPLICATE;
+        q.phase_mode = lp.t.phase_mode; q.map_mode = MAP_IDENTITY; q.pad_mode = lp.t.phase_mode == 1 ? PAD_REPLICATE : PAD_ZERO;
         q.Hc = p.Hs; q.Wc = p.Ws; q.Ho = p.Hs; q.Wo = p.Ws;
         if (tc_plan_geometry(q, lp.t, fTH, fMB)) p = q; else lp.use_tc = false;
       } else if (!tc_plan_geometry(p, lp.t, fTH, fMB)) lp.use_tc = false;
