@@ -195,3 +195,26 @@ def test_full_size_1080p_properties():
     out_t = tr.stylize_u8(frames[1:].transpose(1, 2).contiguous().cuda(), "raw_255").cpu().transpose(1, 2)
     mx, psnr = O.u8_metrics(out_t, out[1:])
     assert mx <= MAX_D and psnr >= 50.0, (mx, psnr)
+
+
+@pytest.mark.parametrize("arch", ["johnson", "nst", "reconet"])
+@pytest.mark.parametrize("env", [{"NST_NO_PHASE": "1"}, {"NST_NO_FOLD": "1"},
+                                 {"NST_TC_FORCE": ";".join(f"{i}:3:1" for i in range(16))}])
+def test_kernel_forms_agree(arch, env, monkeypatch):
+    """The sub-pixel (phase) form of upsample+conv / ConvTranspose, the folded image layer and any tile shape
+    are re-formulations of the same layer: switching them off (or forcing 3-row tiles) must not move the
+    uint8 output by more than one level, and both must meet the oracle tolerance."""
+    from oracle import nst_oracle as O
+    frames = synth.synthetic_frames_u8(2, 88, 136, seed=9)
+    model, sd = _model(arch, seed=2)
+    out = model.stylize_u8(frames.cuda(), PRESET[arch]).cpu()
+    for k, v in env.items():
+        monkeypatch.setenv(k, v)
+    alt_model, _ = _model(arch, seed=2)
+    alt = alt_model.stylize_u8(frames.cuda(), PRESET[arch]).cpu()
+    mx, psnr = O.u8_metrics(alt, out)
+    assert mx <= 1 and psnr >= 50.0, (mx, psnr)
+    ref = O.stylize_u8(arch, sd, frames, PRESET[arch])
+    for y in (out, alt):
+        mx, psnr = O.u8_metrics(y, ref)
+        assert mx <= MAX_D and psnr >= MIN_PSNR, (mx, psnr)
