@@ -207,26 +207,27 @@ def run_b200(args):
     value = world * F * args.steps / (ms_total / 1000.0)
 
     # ---- end to end through the public API with host buffers --------------------------------
-    copy_stream = torch.cuda.Stream(dev)
-    chunk = min(F, 16)
+    h2d_stream, d2h_stream = torch.cuda.Stream(dev), torch.cuda.Stream(dev)
+    chunk = min(F, 8)
 
     def e2e_step():
-        # chunked so the H2D of chunk i+1 and the D2H of chunk i-1 overlap the compute of chunk i
-        done = []
+        # chunked so the H2D of chunk i+1 (one stream) and the D2H of chunk i-1 (another: PCIe is full duplex)
+        # overlap the compute of chunk i
+        main = torch.cuda.current_stream()
+        keep = []
         for c0 in range(0, F, chunk):
-            with torch.cuda.stream(copy_stream):
+            with torch.cuda.stream(h2d_stream):
                 x = host_in[c0:c0 + chunk].to(dev, non_blocking=True)
-                ready = torch.cuda.Event(); ready.record(copy_stream)
-            torch.cuda.current_stream().wait_event(ready)
+                ready = torch.cuda.Event(); ready.record(h2d_stream)
+            main.wait_event(ready)
             y = model.stylize_u8(x, preset)
-            fin = torch.cuda.Event(); fin.record()
-            with torch.cuda.stream(copy_stream):
-                copy_stream.wait_event(fin)
+            fin = torch.cuda.Event(); fin.record(main)
+            with torch.cuda.stream(d2h_stream):
+                d2h_stream.wait_event(fin)
                 host_out[c0:c0 + chunk].copy_(y, non_blocking=True)
-            x.record_stream(torch.cuda.current_stream()); y.record_stream(copy_stream)
-            done.append((x, y))
-        copy_stream.synchronize()
-        torch.cuda.current_stream().synchronize()
+            x.record_stream(main); y.record_stream(d2h_stream)
+            keep.append((x, y))
+        h2d_stream.synchronize(); d2h_stream.synchronize(); main.synchronize()
 
     e2e_step()
     barrier()
