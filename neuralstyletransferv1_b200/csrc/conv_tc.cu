@@ -193,9 +193,9 @@ __device__ __forceinline__ TileCoord decode_tile(const TcPlan& t, int tile) {
   TileCoord c;
   c.n = tile / per_img;
   const int r = tile - c.n * per_img;
-  const int tyi = r / t.tiles_x;
-  c.ty0 = tyi * t.TH;
-  c.tx0 = (r - tyi * t.tiles_x) * t.TW;
+  const int txi = r / t.tiles_y;                     // column-major: the next tile is the one below
+  c.ty0 = (r - txi * t.tiles_y) * t.TH;
+  c.tx0 = txi * t.TW;
   return c;
 }
 
@@ -340,7 +340,7 @@ __device__ __forceinline__ void prod_load(ProdBatch<HAS_RESID, PU>& B, const Pro
 
 template <bool HAS_RESID, int PU>
 __device__ void produce_act16(const ConvParams& p, const TcPlan& t, uint8_t* smem_a, int* srcpix, float2* coeff, uint32_t bar_a_full0,
-                              uint32_t bar_a_empty0, unsigned int* err, unsigned long long* prof, int first_tile, int tile_step, int ptid) {
+                              uint32_t bar_a_empty0, unsigned int* err, unsigned long long* prof, int first_tile, int tile_step, int end_tile, int ptid) {
   const int planes = t.planes;
   const int pshift = planes == 4 ? 2 : (planes == 2 ? 1 : 0);
   const int g = ptid & (planes - 1);
@@ -353,7 +353,7 @@ __device__ void produce_act16(const ConvParams& p, const TcPlan& t, uint8_t* sme
   __half* side = (__half*)p.side_out;
 
   auto build_table = [&](int tile, uint32_t tb) {
-    if (tile >= t.num_tiles) return;
+    if (tile >= end_tile) return;
     const TileCoord tc = decode_tile(t, tile);
     int* tbl = srcpix + tb * tbl_stride;
     for (int q = ptid; q < t.NPOS; q += TC_PROD_THREADS) tbl[q] = locate(p, t, tc, q);
@@ -448,18 +448,18 @@ __device__ void produce_act16(const ConvParams& p, const TcPlan& t, uint8_t* sme
   build_table(first_tile, 0u);
   named_bar_sync(2, TC_PROD_THREADS);
   ProdBatch<HAS_RESID, PU> B0, B1;
-  prod_load<HAS_RESID, PU>(B0, cur, cur.tile < t.num_tiles, p, t, srcpix, tbl_stride, ptid, pshift, g, nitems);
-  while (cur.tile < t.num_tiles) {
+  prod_load<HAS_RESID, PU>(B0, cur, cur.tile < end_tile, p, t, srcpix, tbl_stride, ptid, pshift, g, nitems);
+  while (cur.tile < end_tile) {
     ProdCursor nxt = cur;
     advance(nxt);
     tile_begin(cur);
-    prod_load<HAS_RESID, PU>(B1, nxt, nxt.tile < t.num_tiles, p, t, srcpix, tbl_stride, ptid, pshift, g, nitems);
+    prod_load<HAS_RESID, PU>(B1, nxt, nxt.tile < end_tile, p, t, srcpix, tbl_stride, ptid, pshift, g, nitems);
     process(B0, cur);
     cur = nxt;
-    if (cur.tile >= t.num_tiles) break;
+    if (cur.tile >= end_tile) break;
     advance(nxt);
     tile_begin(cur);
-    prod_load<HAS_RESID, PU>(B0, nxt, nxt.tile < t.num_tiles, p, t, srcpix, tbl_stride, ptid, pshift, g, nitems);
+    prod_load<HAS_RESID, PU>(B0, nxt, nxt.tile < end_tile, p, t, srcpix, tbl_stride, ptid, pshift, g, nitems);
     process(B1, cur);
     cur = nxt;
   }
@@ -483,7 +483,7 @@ struct MmaCtx {
   const uint32_t* ent_tab;
   unsigned int* err;
   unsigned long long* prof;
-  int first_tile, tile_step;
+  int first_tile, tile_step, end_tile;
 };
 
 template <int K16, int MB_>
@@ -497,7 +497,7 @@ __device__ __noinline__ void mma_role(const TcPlan& t, const MmaCtx c) {
   const uint32_t a_stage16 = t.a_stage_bytes >> 4, b_stage16 = t.b_stage_bytes >> 4;
   const uint32_t a_term16 = t.a_term_bytes >> 4, b_term16 = t.b_term_bytes >> 4, b_ent16 = t.b_ent_bytes >> 4;
   const int MB = MB_ ? MB_ : t.MB, NPAD = t.NPAD, k16 = t.k16_per_ent, nterms = t.nterms, tg = t.tg, nent = t.nent;
-  const int nchunks = t.nchunks, ngroups = t.ngroups, num_tiles = t.num_tiles, dbg = t.dbg;
+  const int nchunks = t.nchunks, ngroups = t.ngroups, num_tiles = c.end_tile, dbg = t.dbg;
   const bool resident = t.b_resident != 0;
   const uint32_t a_stages = (uint32_t)t.a_stages, b_stages = (uint32_t)t.b_stages;
   const uint32_t A_FULL0 = c.bar0, A_EMPTY0 = c.bar0 + 8u * TC_MAX_A_STAGES, B_FULL0 = c.bar0 + 8u * (2 * TC_MAX_A_STAGES),
@@ -580,7 +580,7 @@ __device__ __noinline__ void mma_role_phase(const TcPlan& t, const MmaCtx c) {
   const uint32_t a_stage16 = t.a_stage_bytes >> 4, b_stage16 = t.b_stage_bytes >> 4;
   const int MB = MB_ ? MB_ : t.MB, NPAD = t.NPAD, k16 = t.k16_per_ent;
   const uint32_t P = (uint32_t)t.P, cout = (uint32_t)(t.NPAD >> 2), planes = (uint32_t)t.planes;
-  const int nchunks = t.nchunks, ngroups = t.ngroups, num_tiles = t.num_tiles;
+  const int nchunks = t.nchunks, ngroups = t.ngroups, num_tiles = c.end_tile;
   const uint32_t a_stages = (uint32_t)t.a_stages, b_stages = (uint32_t)t.b_stages;
   const uint32_t A_FULL0 = c.bar0, A_EMPTY0 = c.bar0 + 8u * TC_MAX_A_STAGES, B_FULL0 = c.bar0 + 8u * (2 * TC_MAX_A_STAGES),
                  B_EMPTY0 = B_FULL0 + 8u * TC_MAX_B_STAGES, ACC_FULL0 = B_FULL0 + 8u * (2 * TC_MAX_B_STAGES), ACC_EMPTY0 = ACC_FULL0 + 16u;
@@ -681,8 +681,11 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
-  const int first_tile = blockIdx.x;
-  const int tile_step = gridDim.x;
+  // Each CTA walks a contiguous run of tiles; tiles are numbered column-major inside a frame (decode_tile), so consecutive tiles
+  // of a CTA are vertical neighbours (halo rows are shared, statistics are flushed once per frame run, L2 sees nearby rows).
+  const int first_tile = (int)((long long)blockIdx.x * t.num_tiles / gridDim.x);
+  const int end_tile = (int)((long long)(blockIdx.x + 1) * t.num_tiles / gridDim.x);
+  const int tile_step = 1;
 
   if (warp == 0) {
     // =========================== weight loader ===========================
@@ -697,7 +700,7 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
           bulk_g2s(smem_u32(smem_b + (size_t)g * t.b_stage_bytes), wp + (size_t)g * t.b_stage_bytes, t.b_stage_bytes, B_FULL(g));
         }
       } else
-      for (int tile = first_tile; tile < t.num_tiles; tile += tile_step) {
+      for (int tile = first_tile; tile < end_tile; tile += tile_step) {
         for (int g = 0; g < nstage_per_tile; ++g) {
           mbar_wait(B_EMPTY(sb), pb ^ 1u, err, 1, wprof);
           if (t.dbg & 8) { mbar_arrive(B_FULL(sb)); if (++sb == (uint32_t)t.b_stages) { sb = 0; pb ^= 1u; } continue; }
@@ -714,7 +717,7 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
     for (int i = lane; i < t.nent; i += 32) ent_tab[i] = (uint32_t)t.ent_off[i];
     if (t.phase_mode && lane < 16) ent_tab[32 + lane] = t.ent_info[lane];
     __syncwarp();
-    const MmaCtx mc = {smem_u32(smem_a), smem_u32(smem_b), bar0, tmem_base, ent_tab, err, args.prof, first_tile, tile_step};
+    const MmaCtx mc = {smem_u32(smem_a), smem_u32(smem_b), bar0, tmem_base, ent_tab, err, args.prof, first_tile, tile_step, end_tile};
     if (t.phase_mode) {
       if (t.phase_mode == 1 && t.k16_per_ent == 2 && t.MB == 1) mma_role_phase<1, 2, 1>(t, mc);
       else if (t.phase_mode == 1 && t.k16_per_ent == 2 && t.MB == 2) mma_role_phase<1, 2, 2>(t, mc);
@@ -744,7 +747,7 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
       const float b0 = p.bias[0], b1 = p.bias[1], b2 = p.bias[2];
       uint32_t it = 0;
       WaitProf wprof; wprof.init(args.prof);
-      for (int tile = first_tile; tile < ((t.dbg & 32) ? 0 : t.num_tiles); tile += tile_step, ++it) {
+      for (int tile = first_tile; tile < ((t.dbg & 32) ? 0 : end_tile); tile += tile_step, ++it) {
         const TileCoord tc = decode_tile(t, tile);
         const uint32_t buf = it & 1u;
         mbar_wait(ACC_FULL(buf), (it >> 1) & 1u, err, 5, wprof);
@@ -801,7 +804,7 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
       const float inv_p = 1.0f / (float)t.P;
       uint32_t it = 0;
       WaitProf wprof; wprof.init(args.prof);
-      for (int tile = first_tile; tile < ((t.dbg & 32) ? 0 : t.num_tiles); tile += tile_step, ++it) {
+      for (int tile = first_tile; tile < ((t.dbg & 32) ? 0 : end_tile); tile += tile_step, ++it) {
         const TileCoord tc = decode_tile(t, tile);
         if (tc.n != cur_n) { flush(); cur_n = tc.n; }
         const uint32_t buf = it & 1u;
@@ -907,10 +910,10 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
     int cur_n = -1;
     if (t.dbg & 16) {
     } else if (nhwc && p.act16) {
-      if (has_resid) produce_act16<true, 4>(p, t, smem_a, srcpix, coeff, A_FULL(0), A_EMPTY(0), err, args.prof, first_tile, tile_step, ptid);
-      else produce_act16<false, 4>(p, t, smem_a, srcpix, coeff, A_FULL(0), A_EMPTY(0), err, args.prof, first_tile, tile_step, ptid);
+      if (has_resid) produce_act16<true, 4>(p, t, smem_a, srcpix, coeff, A_FULL(0), A_EMPTY(0), err, args.prof, first_tile, tile_step, end_tile, ptid);
+      else produce_act16<false, 4>(p, t, smem_a, srcpix, coeff, A_FULL(0), A_EMPTY(0), err, args.prof, first_tile, tile_step, end_tile, ptid);
     } else
-    for (int tile = first_tile; tile < t.num_tiles; tile += tile_step) {
+    for (int tile = first_tile; tile < end_tile; tile += tile_step) {
       const TileCoord tc = decode_tile(t, tile);
       named_bar_sync(1, TC_PROD_THREADS);          // every producer is done with the previous tile's tables
       if (nhwc && tc.n != cur_n) {
