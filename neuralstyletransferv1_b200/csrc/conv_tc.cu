@@ -813,14 +813,18 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
         const uint32_t tbase = tmem_base + ((uint32_t)(quad * 32) << 16) + buf * (uint32_t)(t.MB * t.NPAD);
         if (p.out_fmt == OUT_F32_NHWC_STATS) {
           const int nmb = (t.dbg & 4) ? 0 : t.MB;
-          for (int jc = 0; jc < njc; ++jc) {
-            // 16 channels at a time: rows of all M blocks are accumulated per lane first, then ONE butterfly
-            // (16 -> 8 -> 4 -> 2 -> 1 live channels per step) reduces over the 32 lanes.
+          const int nph = p.phase_mode ? 4 : 1;                             // sub-pixel layers: column = phase*Cout + co
+          const int ncg = p.phase_mode ? (p.Cout >> 4) : njc;               // 16-channel groups of the OUTPUT tensor
+          for (int cg = 0; cg < ncg; ++cg) {
+            // 16 channels at a time: the rows of every M block (and of the four sub-pixel phases, which feed the same
+            // channel statistics) are accumulated per lane first, then ONE butterfly (16 -> 8 -> 4 -> 2 -> 1 live
+            // channels per step) reduces over the 32 lanes.
             float s[16], q[16];
 #pragma unroll
             for (int i = 0; i < 16; ++i) { s[i] = 0.f; q[i] = 0.f; }
-            const int ph = p.phase_mode ? (jc * 16) / p.Cout : 0;           // sub-pixel layers: column = phase*Cout + co
-            const int co0 = jc * 16 - ph * p.Cout;
+            const int co0 = cg * 16;
+            for (int ph = 0; ph < nph; ++ph) {
+            const int jc = p.phase_mode ? ((ph * p.Cout) >> 4) + cg : cg;
             for (int mb = 0; mb < nmb; ++mb) {
               const int m = mb * 128 + quad * 32 + lane;
               const int ty = (int)(((float)m + 0.5f) * inv_p);
@@ -851,7 +855,8 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
                 for (int i = 0; i < 16; ++i) { s[i] += v[i]; q[i] = fmaf(v[i], v[i], q[i]); }
               }
             }
-            if (jc == njc - 1 && nmb > 0) { tc_fence_before(); mbar_arrive(ACC_EMPTY(buf)); }
+            }
+            if (cg == ncg - 1 && nmb > 0) { tc_fence_before(); mbar_arrive(ACC_EMPTY(buf)); }
 #pragma unroll
             for (int w = 8, off = 16; w >= 1; w >>= 1, off >>= 1) {
               const bool up = (lane & off) != 0;
@@ -874,7 +879,7 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
               *w2 = cur;
             }
           }
-          if (njc == 0 || nmb == 0) { tc_fence_before(); mbar_arrive(ACC_EMPTY(buf)); }
+          if (ncg == 0 || nmb == 0) { tc_fence_before(); mbar_arrive(ACC_EMPTY(buf)); }
         } else {
           for (int mb = 0; mb < t.MB; ++mb) {
             const int m = mb * 128 + quad * 32 + lane;
