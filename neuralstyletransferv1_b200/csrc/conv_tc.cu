@@ -209,14 +209,16 @@ constexpr int SIDE_BIT = 1 << 30;
 __device__ __forceinline__ int locate(const ConvParams& p, const TcPlan& t, const TileCoord& tc, int q) {
   int hy, hx;
   bool filler = false;
+  // divisions by the (runtime) pitch as float multiplies: exact for q < 2^20 (error 2^-24 * q / P << 0.5 / P)
+  const float inv_p = 1.0f / (float)t.P;
   if (p.stride == 1) {
-    hy = q / t.P;
+    hy = (int)(((float)q + 0.5f) * inv_p);
     hx = q - hy * t.P;
     filler = hy >= t.halo_h;
   } else {
-    const int sub = q / t.SUBPOS;
+    const int sub = (int)(((float)q + 0.5f) * (1.0f / (float)t.SUBPOS));
     const int rem = q - sub * t.SUBPOS;
-    const int i = rem / t.P;
+    const int i = (int)(((float)rem + 0.5f) * inv_p);
     const int j = rem - i * t.P;
     hy = 2 * i + (sub >> 1);
     hx = 2 * j + (sub & 1);
