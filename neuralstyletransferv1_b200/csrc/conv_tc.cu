@@ -182,6 +182,13 @@ __device__ __forceinline__ uint32_t pack2(float a, float b, int is_bf16) {
   }
   return r;
 }
+// same with ReLU folded into the conversion (max commutes with round-to-nearest, 0 is exact)
+__device__ __forceinline__ uint32_t pack2_relu(float a, float b, int is_bf16) {
+  uint32_t r;
+  if (is_bf16) asm("cvt.rn.relu.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(b), "f"(a));
+  else asm("cvt.rn.relu.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(b), "f"(a));
+  return r;
+}
 __device__ __forceinline__ float2 unpack2(uint32_t u, int is_bf16) {
   if (is_bf16) return __bfloat1622float2(*reinterpret_cast<__nv_bfloat162*>(&u));
   return __half22float2(*reinterpret_cast<__half2*>(&u));
@@ -340,7 +347,8 @@ __device__ __forceinline__ void prod_load(ProdBatch<HAS_RESID, PU>& B, const Pro
   }
 }
 
-template <bool HAS_RESID, int PU>
+// MODE: 0 = ReLU positions taken from the layer at run time, 1 = no ReLU anywhere, 2 = only a final ReLU (folded into the pack)
+template <bool HAS_RESID, int PU, int MODE>
 __device__ void produce_act16(const ConvParams& p, const TcPlan& t, uint8_t* smem_a, int* srcpix, float2* coeff, uint32_t bar_a_full0,
                               uint32_t bar_a_empty0, unsigned int* err, unsigned long long* prof, int first_tile, int tile_step, int end_tile, int ptid) {
   const int planes = t.planes;
@@ -410,10 +418,15 @@ __device__ void produce_act16(const ConvParams& p, const TcPlan& t, uint8_t* sme
 #pragma unroll
       for (int i = 0; i < 4; ++i) {
         const float2 av = unpack2(aw[i], 0);
-        float v0 = fmaxf(fmaf(av.x, sc[2 * i], sh[2 * i]), lo1);
-        float v1 = fmaxf(fmaf(av.y, sc[2 * i + 1], sh[2 * i + 1]), lo1);
-        if (HAS_RESID) { const float2 rv = unpack2(rw[i], 0); v0 = fmaxf(v0 + rv.x, lo2); v1 = fmaxf(v1 + rv.y, lo2); }
-        hi[u][i] = B.ent[u] >= 0 ? pack2(v0, v1, is_bf16) : 0u;
+        float v0 = fmaf(av.x, sc[2 * i], sh[2 * i]);
+        float v1 = fmaf(av.y, sc[2 * i + 1], sh[2 * i + 1]);
+        if (MODE == 0) { v0 = fmaxf(v0, lo1); v1 = fmaxf(v1, lo1); }
+        if (HAS_RESID) {
+          const float2 rv = unpack2(rw[i], 0);
+          v0 += rv.x; v1 += rv.y;
+          if (MODE == 0) { v0 = fmaxf(v0, lo2); v1 = fmaxf(v1, lo2); }
+        }
+        hi[u][i] = B.ent[u] >= 0 ? (MODE == 2 ? pack2_relu(v0, v1, is_bf16) : pack2(v0, v1, is_bf16)) : 0u;
       }
     }
 #pragma unroll
@@ -917,8 +930,15 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
     int cur_n = -1;
     if (t.dbg & 16) {
     } else if (nhwc && p.act16) {
-      if (has_resid) produce_act16<true, 4>(p, t, smem_a, srcpix, coeff, A_FULL(0), A_EMPTY(0), err, args.prof, first_tile, tile_step, end_tile, ptid);
-      else produce_act16<false, 4>(p, t, smem_a, srcpix, coeff, A_FULL(0), A_EMPTY(0), err, args.prof, first_tile, tile_step, end_tile, ptid);
+#define NST_PRODUCE(R, M) produce_act16<R, 4, M>(p, t, smem_a, srcpix, coeff, A_FULL(0), A_EMPTY(0), err, args.prof, first_tile, tile_step, end_tile, ptid)
+      if (has_resid) {
+        if (!p.pre_relu && !p.post_relu) NST_PRODUCE(true, 1);
+        else if (!p.pre_relu) NST_PRODUCE(true, 2);
+        else NST_PRODUCE(true, 0);
+      } else {
+        if (p.pre_relu || p.post_relu) NST_PRODUCE(false, 2); else NST_PRODUCE(false, 1);
+      }
+#undef NST_PRODUCE
     } else
     for (int tile = first_tile; tile < end_tile; tile += tile_step) {
       const TileCoord tc = decode_tile(t, tile);
