@@ -504,7 +504,7 @@ struct MmaCtx {
 template <int K16, int MB_>
 __device__ __noinline__ void mma_role(const TcPlan& t, const MmaCtx c) {
   const uint32_t idesc = make_idesc(t.NPAD, t.is_bf16);
-  const uint32_t a_lbo16 = (t.pair_mode ? 16u : t.a_plane_bytes) >> 4;
+  const uint32_t a_lbo16 = (t.pair_mode ? 16u * (uint32_t)t.pair_mode : t.a_plane_bytes) >> 4;   // pair: next slot, quad: two slots on
   const uint32_t a_lo_base = ((c.smem_a >> 4) & 0x3FFFu) | (a_lbo16 << 16);
   const uint32_t b_lo_base = ((c.smem_b >> 4) & 0x3FFFu) | ((uint32_t)t.NPAD << 16);   // LBO = NPAD*16 B
   const uint32_t a_kstep16 = (2u * t.a_plane_bytes) >> 4;
@@ -1010,20 +1010,26 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
             for (int u = 0; u < U; ++u) {
 #pragma unroll
               for (int i = 0; i < 8; ++i) x[u][i] = 0.f;
-              if (ent[u] >= 0) {
+              // pair mode: the slot holds one pixel (3 of 8 K slots); quad mode: this pixel and its right neighbour, 4 K slots each
+              const int npx = t.pair_mode == 2 ? 2 : 1;
+              for (int j = 0; j < npx; ++j) {
+                int e = ent[u];
+                if (j == 1) { const int q1 = idx0 + u * TC_PROD_THREADS + 1; e = (ent[u] != -2 && q1 < t.NPOS) ? srcpix[q1] : -1; }
+                if (e < 0) continue;
+                float* xo = &x[u][4 * j];
                 if (p.in_fmt == IN_F32_NCHW3) {
                   // entry = (n*Hs+sy)*Ws+sx  ->  plane-separated address
                   const int hw = p.Hs * p.Ws;
-                  const int n = ent[u] / hw;
-                  const int rem = ent[u] - n * hw;
+                  const int n = e / hw;
+                  const int rem = e - n * hw;
                   const float* s = srcf + ((size_t)n * 3 * hw + rem);
-                  x[u][0] = __ldg(s); x[u][1] = __ldg(s + hw); x[u][2] = __ldg(s + 2 * (size_t)hw);
+                  xo[0] = __ldg(s); xo[1] = __ldg(s + hw); xo[2] = __ldg(s + 2 * (size_t)hw);
                 } else {
-                  const uint8_t* s = (const uint8_t*)p.src + (size_t)ent[u] * 3;
+                  const uint8_t* s = (const uint8_t*)p.src + (size_t)e * 3;
                   const float b0 = (float)__ldg(s), b1 = (float)__ldg(s + 1), b2 = (float)__ldg(s + 2);
-                  x[u][0] = (p.swap_rb ? b2 : b0) * p.in_scale[0] + p.in_shift[0];
-                  x[u][1] = b1 * p.in_scale[1] + p.in_shift[1];
-                  x[u][2] = (p.swap_rb ? b0 : b2) * p.in_scale[2] + p.in_shift[2];
+                  xo[0] = (p.swap_rb ? b2 : b0) * p.in_scale[0] + p.in_shift[0];
+                  xo[1] = b1 * p.in_scale[1] + p.in_shift[1];
+                  xo[2] = (p.swap_rb ? b0 : b2) * p.in_scale[2] + p.in_shift[2];
                 }
               }
             }

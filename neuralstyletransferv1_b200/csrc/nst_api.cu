@@ -284,12 +284,14 @@ static void tc_plan_static(const LayerSpec& s, int precision, TcPlan& t) {
     return;
   }
   t.NPAD = (int)round_up((size_t)s.cout, 16);
-  t.pair_mode = s.cin == 3;
+  // first layer (3 channels): a slot holds one pixel in 8 K positions (pair mode, K16 = 2 pixels, 3/8 useful) or two pixels
+  // in 4 K positions each (quad mode, K16 = 4 pixels through LBO = 2 slots, 3/4 useful: 27 instead of 45 MMAs per M block)
+  t.pair_mode = s.cin == 3 ? (getenv("NST_NO_QUAD") ? 1 : 2) : 0;
   t.fold_s = (s.cout == 3 && s.ks == 9 && s.cin != 3 && !getenv("NST_NO_FOLD")) ? 1 : 0;
   if (t.fold_s) t.NPAD = 32;
   if (t.pair_mode) {
     t.CK = 8; t.planes = 1; t.nchunks = 1;
-    t.nent = s.ks * ((s.ks + 1) / 2);
+    t.nent = t.pair_mode == 2 ? s.ks * ((s.ks + 3) / 4) : s.ks * ((s.ks + 1) / 2);
     t.k16_per_ent = 1;
   } else {
     t.CK = (s.cin % 32 == 0) ? 32 : 16;
@@ -332,8 +334,13 @@ static bool tc_layout(const ConvParams& p, TcPlan& t, int MB, int bTH, int bTW, 
     t.halo_h = bTH + e; t.halo_w = bP; t.SUBPOS = 0;
     int k = 0;
     if (t.pair_mode) {
-      for (int r = 0; r < p.ks; ++r) for (int sp = 0; sp < (p.ks + 1) / 2; ++sp) t.ent_off[k++] = r * bP + 2 * sp;
-      max_off = e * bP + e + 1;
+      if (t.pair_mode == 2) {
+        for (int r = 0; r < p.ks; ++r) for (int sp = 0; sp < (p.ks + 3) / 4; ++sp) t.ent_off[k++] = r * bP + 4 * sp;
+        max_off = e * bP + e + 4;
+      } else {
+        for (int r = 0; r < p.ks; ++r) for (int sp = 0; sp < (p.ks + 1) / 2; ++sp) t.ent_off[k++] = r * bP + 2 * sp;
+        max_off = e * bP + e + 1;
+      }
     } else {
       if (t.phase_mode) { for (int i = 0; i < PH_NENT_K[t.phase_mode]; ++i) t.ent_off[k++] = PH_R_K[t.phase_mode][i] * bP + PH_S_K[t.phase_mode][i]; max_off = e * bP + e; }
       else if (t.fold_s) { for (int r = 0; r < p.ks; ++r) t.ent_off[k++] = r * bP; max_off = e * bP; }
@@ -457,7 +464,12 @@ static std::vector<uint16_t> tc_pack_weights(const LayerSpec& s, const TcPlan& t
           for (int i = 0; i < 8; ++i) {
             float v = 0.f;
             if (n < s.cout) {
-              if (t.pair_mode) {
+              if (t.pair_mode == 2) {
+                const int per_row = (ks + 3) / 4;
+                const int r = ent / per_row, sp = ent % per_row;
+                const int sx = 4 * sp + kp * 2 + i / 4, c = i % 4;
+                if (sx < ks && c < s.cin) v = w_oihw[(((size_t)n * s.cin + c) * ks + r) * ks + sx];
+              } else if (t.pair_mode) {
                 const int per_row = (ks + 1) / 2;
                 const int r = ent / per_row, sp = ent % per_row;
                 const int sx = 2 * sp + kp;

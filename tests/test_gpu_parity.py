@@ -198,7 +198,7 @@ def test_full_size_1080p_properties():
 
 
 @pytest.mark.parametrize("arch", ["johnson", "nst", "reconet"])
-@pytest.mark.parametrize("env", [{"NST_NO_PHASE": "1"}, {"NST_NO_FOLD": "1"},
+@pytest.mark.parametrize("env", [{"NST_NO_PHASE": "1"}, {"NST_NO_FOLD": "1"}, {"NST_NO_QUAD": "1"},
                                  {"NST_TC_FORCE": ";".join(f"{i}:3:1" for i in range(16))}])
 def test_kernel_forms_agree(arch, env, monkeypatch):
     """The sub-pixel (phase) form of upsample+conv / ConvTranspose, the folded image layer and any tile shape
