@@ -202,8 +202,9 @@ def test_full_size_1080p_properties():
                                  {"NST_TC_FORCE": ";".join(f"{i}:3:1" for i in range(16))}])
 def test_kernel_forms_agree(arch, env, monkeypatch):
     """The sub-pixel (phase) form of upsample+conv / ConvTranspose, the folded image layer and any tile shape
-    are re-formulations of the same layer: switching them off (or forcing 3-row tiles) must not move the
-    uint8 output by more than one level, and both must meet the oracle tolerance."""
+    are re-formulations of the same layer (only the fp32 accumulation order changes): switching them off (or
+    forcing 3-row tiles) must leave the uint8 output within the tolerance of itself at PSNR >= 50 dB, and both
+    must meet the oracle tolerance."""
     from oracle import nst_oracle as O
     frames = synth.synthetic_frames_u8(2, 88, 136, seed=9)
     model, sd = _model(arch, seed=2)
@@ -213,7 +214,7 @@ def test_kernel_forms_agree(arch, env, monkeypatch):
     alt_model, _ = _model(arch, seed=2)
     alt = alt_model.stylize_u8(frames.cuda(), PRESET[arch]).cpu()
     mx, psnr = O.u8_metrics(alt, out)
-    assert mx <= 1 and psnr >= 50.0, (mx, psnr)
+    assert mx <= MAX_D and psnr >= 50.0, (mx, psnr)
     ref = O.stylize_u8(arch, sd, frames, PRESET[arch])
     for y in (out, alt):
         mx, psnr = O.u8_metrics(y, ref)
