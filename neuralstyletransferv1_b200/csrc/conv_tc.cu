@@ -939,6 +939,71 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
         if (p.pre_relu || p.post_relu) NST_PRODUCE(false, 2); else NST_PRODUCE(false, 1);
       }
 #undef NST_PRODUCE
+    } else if (p.in_fmt == IN_U8_NHWC3 && t.pair_mode == 2 && p.stride == 1 && t.a_tplanes == 1 && !(t.dbg & 32768)) {
+      // ---- first layer, uint8 frames, quad mode ----
+      // One slot = (pixel q, pixel q+1) x (3 channels + pad).  With a single 8-channel plane nothing amortises a per-position
+      // source table (it was ~70 % of this role's instructions), so the halo is addressed through a row table [halo_h] and a
+      // column table [P] built per tile (reflection / pre-pad folded in), and 8 slots of raw bytes are in flight per thread.
+      int* rowv = srcpix;
+      int* colv = srcpix + 128;                       // halo_h <= 72 rows
+      const float inv_p = 1.0f / (float)t.P;
+      constexpr int UB = 8;
+      for (int tile = first_tile; tile < end_tile; tile += tile_step) {
+        const TileCoord tc = decode_tile(t, tile);
+        named_bar_sync(1, TC_PROD_THREADS);          // every producer is done with the previous tile's tables
+        if (ptid < t.halo_h) {
+          const int sy = map_coord((tc.ty0 + p.oy_off) + ptid - p.pad_t, p.Hc, p.Hs, p.map_mode, p.prepad, p.pad_mode);
+          rowv[ptid] = sy < 0 ? -1 : (tc.n * p.Hs + sy) * p.Ws;
+        }
+        for (int j = ptid - 64; j >= 0 && j < t.P; j += TC_PROD_THREADS - 64)
+          colv[j] = map_coord((tc.tx0 + p.ox_off) + j - p.pad_l, p.Wc, p.Ws, p.map_mode, p.prepad, p.pad_mode);
+        named_bar_sync(2, TC_PROD_THREADS);
+        mbar_wait(A_EMPTY(sa), pa ^ 1u, err, 6);
+        uint8_t* plane = smem_a + (size_t)sa * t.a_stage_bytes;
+        const uint8_t* __restrict__ src8 = (const uint8_t*)p.src;
+        for (int q0 = ptid; q0 < t.NPOS; q0 += UB * TC_PROD_THREADS) {
+          uint32_t raw[UB][2];
+#pragma unroll
+          for (int u = 0; u < UB; ++u) {
+            const int q = q0 + u * TC_PROD_THREADS;
+            raw[u][0] = raw[u][1] = 0xFF000000u;                       // top byte set = structural zero
+            if (q < t.NPOS) {
+              const int hy = (int)(((float)q + 0.5f) * inv_p);
+              const int hx = q - hy * t.P;
+              const int rb = hy < t.halo_h ? rowv[hy] : -1;
+#pragma unroll
+              for (int j = 0; j < 2; ++j) {
+                const int cx = (hx + j < t.P) ? colv[hx + j] : -1;
+                if (rb >= 0 && cx >= 0) {
+                  const uint8_t* s8 = src8 + (size_t)(rb + cx) * 3;
+                  raw[u][j] = (uint32_t)__ldg(s8) | ((uint32_t)__ldg(s8 + 1) << 8) | ((uint32_t)__ldg(s8 + 2) << 16);
+                }
+              }
+            }
+          }
+#pragma unroll
+          for (int u = 0; u < UB; ++u) {
+            const int q = q0 + u * TC_PROD_THREADS;
+            if (q >= t.NPOS) continue;
+            uint32_t hw[4];
+#pragma unroll
+            for (int j = 0; j < 2; ++j) {
+              const uint32_t r = raw[u][j];
+              const float b0 = (float)(r & 0xFFu), b1 = (float)((r >> 8) & 0xFFu), b2 = (float)((r >> 16) & 0xFFu);
+              const bool live = (r >> 24) == 0u;
+              const float x0 = (p.swap_rb ? b2 : b0) * p.in_scale[0] + p.in_shift[0];
+              const float x1 = b1 * p.in_scale[1] + p.in_shift[1];
+              const float x2 = (p.swap_rb ? b0 : b2) * p.in_scale[2] + p.in_shift[2];
+              hw[2 * j] = live ? pack2(x0, x1, is_bf16) : 0u;
+              hw[2 * j + 1] = live ? pack2(x2, 0.f, is_bf16) : 0u;
+            }
+            *reinterpret_cast<uint4*>(plane + (size_t)q * 16) = make_uint4(hw[0], hw[1], hw[2], hw[3]);
+          }
+        }
+        fence_proxy_async_smem();
+        mbar_arrive(A_FULL(sa));
+        if (++sa == (uint32_t)t.a_stages) { sa = 0; pa ^= 1u; }
+      }
     } else
     for (int tile = first_tile; tile < end_tile; tile += tile_step) {
       const TileCoord tc = decode_tile(t, tile);
