@@ -70,7 +70,57 @@ __global__ void __launch_bounds__(256) composite_kernel(const __grid_constant__ 
   }
 }
 
+// uint8 fast path: 4 pixels (12 bytes = three 32-bit words per source, one float4 per mask) per thread; same arithmetic.
+__global__ void __launch_bounds__(256) composite_u8x4_kernel(const __grid_constant__ CompositeArgs a) {
+  const size_t hw = (size_t)a.H * a.W;
+  const size_t nq = hw >> 2;
+  for (size_t q = (size_t)blockIdx.x * blockDim.x + threadIdx.x; q < nq; q += (size_t)gridDim.x * blockDim.x) {
+    float acc[12], wsum[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+    for (int i = 0; i < 12; ++i) acc[i] = 0.f;
+    for (int r = 0; r < a.R; ++r) {
+      const float4 m4 = __ldg(reinterpret_cast<const float4*>(a.masks + (size_t)r * hw) + q);
+      const float m[4] = {m4.x, m4.y, m4.z, m4.w};
+      float rb[12];
+#pragma unroll
+      for (int i = 0; i < 12; ++i) rb[i] = 0.f;
+      for (int j = 0; j < a.J; ++j) {
+        const int id = a.idx[r * a.J + j];
+        const float wt = a.w[r * a.J + j];
+        if (wt == 0.f && a.J > 1) continue;
+        const uint32_t* sp = reinterpret_cast<const uint32_t*>(id < 0 ? a.original : a.srcs[id]) + q * 3;   // L1/L2 serve the re-reads
+        const uint32_t w3[3] = {__ldg(sp), __ldg(sp + 1), __ldg(sp + 2)};
+#pragma unroll
+        for (int i = 0; i < 12; ++i) rb[i] += wt * ((float)((w3[i >> 2] >> (8 * (i & 3))) & 0xFFu) / 255.0f);
+      }
+#pragma unroll
+      for (int i = 0; i < 12; ++i) acc[i] += rb[i] * m[i / 3];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) wsum[i] += m[i];
+    }
+    uint32_t o3[3] = {0u, 0u, 0u};
+#pragma unroll
+    for (int i = 0; i < 12; ++i) {
+      const float o = fminf(fmaxf(acc[i] / fmaxf(wsum[i / 3], 1e-6f), 0.f), 1.f);
+      o3[i >> 2] |= (uint32_t)(uint8_t)(o * 255.0f) << (8 * (i & 3));
+    }
+    uint32_t* op = reinterpret_cast<uint32_t*>(a.out) + q * 3;
+    op[0] = o3[0]; op[1] = o3[1]; op[2] = o3[2];
+  }
+}
+
 cudaError_t launch_composite(const CompositeArgs& a, bool u8, cudaStream_t stream) {
+  if (u8 && ((size_t)a.H * a.W) % 4 == 0) {
+    bool aligned = ((uintptr_t)a.out % 4 == 0) && ((uintptr_t)a.masks % 16 == 0) && (a.original == nullptr || (uintptr_t)a.original % 4 == 0);
+    for (int k = 0; k < a.K; ++k) aligned = aligned && ((uintptr_t)a.srcs[k] % 4 == 0);
+    if (aligned) {
+      const size_t nq = (size_t)a.H * a.W / 4;
+      int blocks = (int)((nq + 255) / 256);
+      if (blocks > 148 * 8) blocks = 148 * 8;
+      composite_u8x4_kernel<<<blocks, 256, 0, stream>>>(a);
+      return cudaGetLastError();
+    }
+  }
   const size_t hw = (size_t)a.H * a.W;
   int blocks = (int)((hw + 255) / 256);
   if (blocks > 148 * 16) blocks = 148 * 16;
