@@ -219,3 +219,20 @@ def test_kernel_forms_agree(arch, env, monkeypatch):
     for y in (out, alt):
         mx, psnr = O.u8_metrics(y, ref)
         assert mx <= MAX_D and psnr >= MIN_PSNR, (mx, psnr)
+
+
+def test_composite_u8_odd_size_scalar_path():
+    """H*W not a multiple of 4 takes the one-pixel-per-thread kernel; it must agree with the oracle like the vector path."""
+    import neuralstyletransferv1_b200 as m
+    from oracle import nst_oracle as O
+    g = torch.Generator().manual_seed(11)
+    H, W, K = 7, 9, 3
+    s8 = [torch.randint(0, 256, (H, W, 3), dtype=torch.uint8, generator=g) for _ in range(K)]
+    o8 = torch.randint(0, 256, (H, W, 3), dtype=torch.uint8, generator=g)
+    masks = torch.rand(K, H, W, generator=g)
+    idx = [[0], [1], [-1]]
+    got = m.composite_regions([s.cuda() for s in s8], masks.cuda(), idx, original=o8.cuda()).cpu()
+    sf = [s.permute(2, 0, 1).float() / 255 for s in s8]
+    want = O.composite_regions_advanced(sf, [mk[None, None] for mk in masks], idx, [[1.0]] * 3, o8.permute(2, 0, 1).float() / 255)
+    mx, _ = O.u8_metrics(got, O.pack_u8(want[None])[0])
+    assert mx <= 1, mx
