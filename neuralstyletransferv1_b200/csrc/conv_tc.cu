@@ -808,8 +808,8 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
       auto flush = [&]() {
         if (cur_n < 0 || p.out_fmt != OUT_F32_NHWC_STATS) return;
         __syncwarp();
-        for (int c = lane; c < p.Cout; c += 32) {
-          double* st = p.out_stats + ((size_t)cur_n * p.Cout + c) * 2;
+        for (int c = lane; c < p.co_pass; c += 32) {
+          double* st = p.out_stats + ((size_t)cur_n * p.Cout + p.co_off + c) * 2;
           atomicAdd(st, (double)wstat[2 * c]);
           atomicAdd(st + 1, (double)wstat[2 * c + 1]);
           wstat[2 * c] = 0.f; wstat[2 * c + 1] = 0.f;
@@ -829,7 +829,7 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
         if (p.out_fmt == OUT_F32_NHWC_STATS) {
           const int nmb = (t.dbg & 4) ? 0 : t.MB;
           const int nph = p.phase_mode ? 4 : 1;                             // sub-pixel layers: column = phase*Cout + co
-          const int ncg = p.phase_mode ? (p.Cout >> 4) : njc;               // 16-channel groups of the OUTPUT tensor
+          const int ncg = p.phase_mode ? (p.co_pass >> 4) : njc;               // 16-channel groups of the OUTPUT tensor
           for (int cg = 0; cg < ncg; ++cg) {
             // 16 channels at a time: the rows of every M block (and of the four sub-pixel phases, which feed the same
             // channel statistics) are accumulated per lane first, then ONE butterfly (16 -> 8 -> 4 -> 2 -> 1 live
@@ -839,7 +839,7 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
             for (int i = 0; i < 16; ++i) { s[i] = 0.f; q[i] = 0.f; }
             const int co0 = cg * 16;
             for (int ph = 0; ph < nph; ++ph) {
-            const int jc = p.phase_mode ? ((ph * p.Cout) >> 4) + cg : cg;
+            const int jc = p.phase_mode ? ((ph * p.co_pass) >> 4) + cg : cg;
             for (int mb = 0; mb < nmb; ++mb) {
               const int m = mb * 128 + quad * 32 + lane;
               const int ty = (int)(((float)m + 0.5f) * inv_p);
@@ -850,7 +850,7 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
               tmem_ld16(tbase + (uint32_t)(mb * t.NPAD + jc * 16), v);
               if (valid) {
                 size_t oidx;
-                if (p.phase_mode) oidx = (((size_t)tc.n * (2 * p.Ho) + 2 * oy + (ph >> 1)) * (size_t)(2 * p.Wo) + 2 * ox + (ph & 1)) * p.Cout + co0;
+                if (p.phase_mode) oidx = (((size_t)tc.n * (2 * p.Ho) + 2 * oy + (ph >> 1)) * (size_t)(2 * p.Wo) + 2 * ox + (ph & 1)) * p.Cout + p.co_off + co0;
                 else oidx = (((size_t)tc.n * p.Ho + oy) * p.Wo + ox) * p.Cout + jc * 16;
                 if (p.act16) {
                   uint32_t h[8];

@@ -170,6 +170,8 @@ static std::vector<LayerSpec> reconet_layers() {
 struct LayerDev {
   float* wdir = nullptr;     // [ks*ks][cin][cout] fp32 (direct kernel)
   void* wpack = nullptr;     // tcgen05 operand tiles (16-bit)
+  void* wpack2 = nullptr;    // second half of the output channels (phase layers split in two launches)
+  int nsplit = 1;
   float* bias = nullptr;     // [cout]
   float* in_gamma = nullptr; // [cin]
   float* in_beta = nullptr;  // [cin]
@@ -251,7 +253,7 @@ static bool ph_hits(int kind, int a, int r, int rp) {
 }
 static int phase_kind(const LayerSpec& s, int precision) {
   if (getenv("NST_NO_PHASE") || precision == NST_PREC_F16X3) return 0;
-  if (s.ks != 3 || s.stride != 1 || s.cout % 16 != 0 || 4 * s.cout > 256 || s.cin % 16 != 0) return 0;
+  if (s.ks != 3 || s.stride != 1 || s.cout % 16 != 0 || 4 * s.cout > 256 || s.cin % 16 != 0) return 0;   // (callers pass the per-launch channel count)
   if (s.map_mode == MAP_UP2 && s.pad_mode == PAD_REFLECT) return 1;
   if (s.map_mode == MAP_ZERO_INSERT2 && s.pad_mode == PAD_ZERO) return 2;
   return 0;
@@ -537,7 +539,7 @@ extern "C" int nst_create(int device, int arch, int precision, nst_handle** out)
 }
 
 static void free_layer(LayerDev& d) {
-  cudaFree(d.wdir); cudaFree(d.wpack); cudaFree(d.bias); cudaFree(d.in_gamma); cudaFree(d.in_beta);
+  cudaFree(d.wdir); cudaFree(d.wpack); cudaFree(d.wpack2); cudaFree(d.bias); cudaFree(d.in_gamma); cudaFree(d.in_beta);
   d = LayerDev();
 }
 
@@ -614,10 +616,19 @@ extern "C" int nst_load_weights(nst_handle* h, int n_tensors, const char* const*
     }
     d.tc_ok = h->precision != NST_PREC_FP32_DIRECT && tc_supported(s);
     if (d.tc_ok) {
-      tc_plan_static(s, h->precision, d.tc_static);
+      // a sub-pixel layer whose 4*Cout accumulator columns do not fit TMEM (ReCoNet decoder.layers.1: 4*96) runs as two
+      // launches over half of the output channels each
+      LayerSpec half = s;
+      half.cout = s.cout / 2;
+      d.nsplit = (4 * s.cout > 256 && s.cout % 32 == 0 && phase_kind(half, h->precision) != 0 && !getenv("NST_NO_SPLIT")) ? 2 : 1;
+      const LayerSpec& ps = d.nsplit == 2 ? half : s;
+      tc_plan_static(ps, h->precision, d.tc_static);
       d.tc_static.dbg = h->dbg;
-      std::vector<uint16_t> pk = tc_pack_weights(s, d.tc_static, w);
-      CUDA_TRY(upload((uint16_t**)&d.wpack, pk));
+      for (int part = 0; part < d.nsplit; ++part) {
+        std::vector<float> wpart(w.begin() + (size_t)part * ps.cout * s.cin * s.ks * s.ks, w.begin() + (size_t)(part + 1) * ps.cout * s.cin * s.ks * s.ks);
+        std::vector<uint16_t> pk = tc_pack_weights(ps, d.tc_static, wpart);
+        CUDA_TRY(upload((uint16_t**)(part == 0 ? &d.wpack : &d.wpack2), pk));
+      }
     }
   }
   int unexpected = 0;
@@ -669,6 +680,7 @@ static int make_plan(nst_handle* h, int N, int H, int W) {
     p.pre_relu = s.pre_relu; p.post_relu = s.post_relu; p.tanh_out = s.tanh_out;
     p.blend = 1.f;
     p.act16 = h->act16;
+    p.co_off = 0; p.co_pass = s.cout / h->dev[li].nsplit;
     if (s.src == BUF_IMAGE) { p.Hs = H; p.Ws = W; }
     else {
       const BufDims& bd = h->bufs[s.src];
@@ -835,10 +847,15 @@ static int run_forward(nst_handle* h, const IoSpec& io, int N, int H, int W, voi
         TcArgs a;
         a.p = p; a.t = lp.t;
         a.t.num_tiles = lp.t.tiles_x * lp.t.tiles_y * n;
-        a.wpack = d.wpack; a.err_flag = h->err_dev;
+        a.err_flag = h->err_dev;
+        for (int part = 0; part < d.nsplit; ++part) {
+        a.wpack = part == 0 ? d.wpack : d.wpack2;
+        a.p.co_off = part * a.p.co_pass;
         a.prof = layer_ms ? h->prof_dev : nullptr;
         if (a.prof) CUDA_TRY(cudaMemsetAsync(a.prof, 0, 16 * sizeof(unsigned long long), stream));
         CUDA_TRY(launch_conv_tc(a, h->num_sms, stream));
+        if (part + 1 < d.nsplit) ++h->launches;
+        }
         if (a.prof) {
           unsigned long long pc[16];
           CUDA_TRY(cudaMemcpyAsync(pc, a.prof, sizeof(pc), cudaMemcpyDeviceToHost, stream));

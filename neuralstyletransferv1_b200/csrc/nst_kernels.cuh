@@ -46,6 +46,8 @@ struct ConvParams {
   // ---- output ----
   int Ho, Wo, Cout;         // produced extent
   int oy_off, ox_off;       // produced (0,0) sits at this conv-output coordinate (NST crop)
+  int co_off, co_pass;      // channel split of a phase layer whose 4*Cout columns exceed TMEM: this launch produces output
+                            // channels [co_off, co_off + co_pass) (co_pass = Cout, co_off = 0 for every other layer)
   int phase_mode;           // sub-pixel form of upsample x2 + conv3: (Ho, Wo) is the LOW-RES tile grid, GEMM column = phase*Cout + co,
                             // phase (a,b) of grid position (i,j) is output pixel (2i+a, 2j+b) of the [N, 2Ho, 2Wo, Cout] tensor
   int out_fmt;

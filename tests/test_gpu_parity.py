@@ -60,7 +60,7 @@ def test_all_layers_run_on_tcgen05(arch):
     model.stylize_u8(synth.synthetic_frames_u8(1, 64, 64).cuda(), PRESET[arch])
     kinds = [d["kernel"] for d in model.engine.layer_info()]
     assert all(k == "tcgen05" for k in kinds), kinds
-    assert model.engine.launch_count == len(kinds)
+    assert len(kinds) <= model.engine.launch_count <= len(kinds) + 1      # ReCoNet decoder.layers.1 runs as two channel halves
 
 
 @pytest.mark.parametrize("arch,n,h,w", [("johnson", 1, 64, 64), ("johnson", 3, 120, 200), ("johnson", 2, 272, 480),
@@ -198,7 +198,7 @@ def test_full_size_1080p_properties():
 
 
 @pytest.mark.parametrize("arch", ["johnson", "nst", "reconet"])
-@pytest.mark.parametrize("env", [{"NST_NO_PHASE": "1"}, {"NST_NO_FOLD": "1"}, {"NST_NO_QUAD": "1"},
+@pytest.mark.parametrize("env", [{"NST_NO_PHASE": "1"}, {"NST_NO_FOLD": "1"}, {"NST_NO_QUAD": "1"}, {"NST_NO_SPLIT": "1"},
                                  {"NST_TC_FORCE": ";".join(f"{i}:3:1" for i in range(16))}])
 def test_kernel_forms_agree(arch, env, monkeypatch):
     """The sub-pixel (phase) form of upsample+conv / ConvTranspose, the folded image layer and any tile shape
