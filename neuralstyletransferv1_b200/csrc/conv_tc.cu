@@ -348,7 +348,8 @@ __device__ __forceinline__ void prod_load(ProdBatch<HAS_RESID, PU>& B, const Pro
 }
 
 // MODE: 0 = ReLU positions taken from the layer at run time, 1 = no ReLU anywhere, 2 = only a final ReLU (folded into the pack)
-template <bool HAS_RESID, int PU, int MODE>
+// BF16 / SIDE: operand type and presence of a side output as compile-time facts (a run-time is_bf16 costs a branch per pack)
+template <bool HAS_RESID, int PU, int MODE, bool BF16, bool SIDE>
 __device__ void produce_act16(const ConvParams& p, const TcPlan& t, uint8_t* smem_a, int* srcpix, float2* coeff, uint32_t bar_a_full0,
                               uint32_t bar_a_empty0, unsigned int* err, unsigned long long* prof, int first_tile, int tile_step, int end_tile, int ptid) {
   const int planes = t.planes;
@@ -357,7 +358,7 @@ __device__ void produce_act16(const ConvParams& p, const TcPlan& t, uint8_t* sme
   const int nitems = t.NPOS * planes;
   const int tbl_stride = (t.NPOS + 3) & ~3;
   const int nB = (nitems + PU * TC_PROD_THREADS - 1) / (PU * TC_PROD_THREADS);     // batches per chunk
-  const int is_bf16 = t.is_bf16;
+  constexpr int is_bf16 = BF16 ? 1 : 0;
   const float lo1 = (p.pre_relu || (!HAS_RESID && p.post_relu)) ? 0.f : -INFINITY;   // without a residual add the two ReLUs coincide
   const float lo2 = p.post_relu ? 0.f : -INFINITY;
   __half* side = (__half*)p.side_out;
@@ -433,16 +434,9 @@ __device__ void produce_act16(const ConvParams& p, const TcPlan& t, uint8_t* sme
     for (int u = 0; u < PU; ++u) {
       const int e = B.ent[u];
       const int q = (ptid + (c.b * PU + u) * TC_PROD_THREADS) >> pshift;
-      if (HAS_RESID) {
+      if (SIDE) {
         if (e >= 0 && (e & SIDE_BIT)) {
           // the materialised block input is stored as fp16 -- the same rounding the MMA operand gets
-          uint32_t sv[4];
-#pragma unroll
-          for (int i = 0; i < 4; ++i) { if (is_bf16) { const float2 f = unpack2(hi[u][i], 1); sv[i] = pack2(f.x, f.y, 0); } else sv[i] = hi[u][i]; }
-          *reinterpret_cast<uint4*>(side + (size_t)(e & (SIDE_BIT - 1)) * p.Cin + c0) = make_uint4(sv[0], sv[1], sv[2], sv[3]);
-        }
-      } else if (side != nullptr) {
-        if (e >= 0 && (e & SIDE_BIT)) {
           uint32_t sv[4];
 #pragma unroll
           for (int i = 0; i < 4; ++i) { if (is_bf16) { const float2 f = unpack2(hi[u][i], 1); sv[i] = pack2(f.x, f.y, 0); } else sv[i] = hi[u][i]; }
@@ -930,7 +924,8 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
     int cur_n = -1;
     if (t.dbg & 16) {
     } else if (nhwc && p.act16) {
-#define NST_PRODUCE(R, M) produce_act16<R, 4, M>(p, t, smem_a, srcpix, coeff, A_FULL(0), A_EMPTY(0), err, args.prof, first_tile, tile_step, end_tile, ptid)
+#define NST_PRODUCE4(R, M, B, S) produce_act16<R, 4, M, B, S>(p, t, smem_a, srcpix, coeff, A_FULL(0), A_EMPTY(0), err, args.prof, first_tile, tile_step, end_tile, ptid)
+#define NST_PRODUCE(R, M) do { if (t.is_bf16) NST_PRODUCE4(R, 0, true, true); else if (p.side_out != nullptr) NST_PRODUCE4(R, M, false, true); else NST_PRODUCE4(R, M, false, false); } while (0)
       if (has_resid) {
         if (!p.pre_relu && !p.post_relu) NST_PRODUCE(true, 1);
         else if (!p.pre_relu) NST_PRODUCE(true, 2);
@@ -938,6 +933,7 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
       } else {
         if (p.pre_relu || p.post_relu) NST_PRODUCE(false, 2); else NST_PRODUCE(false, 1);
       }
+#undef NST_PRODUCE4
 #undef NST_PRODUCE
     } else if (p.in_fmt == IN_U8_NHWC3 && t.pair_mode == 2 && p.stride == 1 && t.a_tplanes == 1 && !(t.dbg & 32768)) {
       // ---- first layer, uint8 frames, quad mode ----
