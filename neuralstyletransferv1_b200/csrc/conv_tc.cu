@@ -323,14 +323,14 @@ struct ProdCursor {
 
 template <bool HAS_RESID, int PU>
 __device__ __forceinline__ void prod_load(ProdBatch<HAS_RESID, PU>& B, const ProdCursor& c, bool valid, const ConvParams& p, const TcPlan& t,
-                                          const int* srcpix, int tbl_stride, int ptid, int pshift, int g, int nitems) {
+                                          const int* srcpix, int tbl_stride, int ptid, int pshift, int g, int nitems, int PT) {
   const __half* __restrict__ src = (const __half*)p.src;
   const __half* __restrict__ res = (const __half*)p.resid;
   const int* tbl = srcpix + c.tb * tbl_stride;
   const int c0 = c.ch * t.CK + g * 8;
 #pragma unroll
   for (int u = 0; u < PU; ++u) {
-    const int idx = ptid + (c.b * PU + u) * TC_PROD_THREADS;
+    const int idx = ptid + (c.b * PU + u) * PT;
     B.ent[u] = (valid && idx < nitems && !(t.dbg & 2)) ? tbl[idx >> pshift] : -2;
   }
 #pragma unroll
@@ -352,12 +352,13 @@ __device__ __forceinline__ void prod_load(ProdBatch<HAS_RESID, PU>& B, const Pro
 template <bool HAS_RESID, int PU, int MODE, bool BF16, bool SIDE>
 __device__ void produce_act16(const ConvParams& p, const TcPlan& t, uint8_t* smem_a, int* srcpix, float2* coeff, uint32_t bar_a_full0,
                               uint32_t bar_a_empty0, unsigned int* err, unsigned long long* prof, int first_tile, int tile_step, int end_tile, int ptid) {
+  const int PT = t.prod_warps * 32;          // producer threads of this layer (8 or 10 warps, chosen per layer on the host)
   const int planes = t.planes;
   const int pshift = planes == 4 ? 2 : (planes == 2 ? 1 : 0);
   const int g = ptid & (planes - 1);
   const int nitems = t.NPOS * planes;
   const int tbl_stride = (t.NPOS + 3) & ~3;
-  const int nB = (nitems + PU * TC_PROD_THREADS - 1) / (PU * TC_PROD_THREADS);     // batches per chunk
+  const int nB = (nitems + PU * PT - 1) / (PU * PT);     // batches per chunk
   constexpr int is_bf16 = BF16 ? 1 : 0;
   const float lo1 = (p.pre_relu || (!HAS_RESID && p.post_relu)) ? 0.f : -INFINITY;   // without a residual add the two ReLUs coincide
   const float lo2 = p.post_relu ? 0.f : -INFINITY;
@@ -367,7 +368,7 @@ __device__ void produce_act16(const ConvParams& p, const TcPlan& t, uint8_t* sme
     if (tile >= end_tile) return;
     const TileCoord tc = decode_tile(t, tile);
     int* tbl = srcpix + tb * tbl_stride;
-    for (int q = ptid; q < t.NPOS; q += TC_PROD_THREADS) tbl[q] = locate(p, t, tc, q);
+    for (int q = ptid; q < t.NPOS; q += PT) tbl[q] = locate(p, t, tc, q);
   };
   auto advance = [&](ProdCursor& c) {
     if (++c.b == nB) {
@@ -386,10 +387,10 @@ __device__ void produce_act16(const ConvParams& p, const TcPlan& t, uint8_t* sme
   // first read by the prefetch that follows), refresh the per-sample norm coefficients
   auto tile_begin = [&](const ProdCursor& c) {
     if (c.b != 0 || c.ch != 0) return;
-    named_bar_sync(1, TC_PROD_THREADS);
+    named_bar_sync(1, PT);
     const int n = c.tile / (t.tiles_x * t.tiles_y);
     if (n != cur_n) {
-      for (int ch = ptid; ch < p.Cin; ch += TC_PROD_THREADS) {
+      for (int ch = ptid; ch < p.Cin; ch += PT) {
         float s_, h_;
         norm_coeff(p, n, ch, s_, h_);
         coeff[ch] = make_float2(s_, h_);
@@ -397,7 +398,7 @@ __device__ void produce_act16(const ConvParams& p, const TcPlan& t, uint8_t* sme
       cur_n = n;
     }
     build_table(c.tile + tile_step, c.tb ^ 1u);
-    named_bar_sync(2, TC_PROD_THREADS);
+    named_bar_sync(2, PT);
   };
   auto process = [&](const ProdBatch<HAS_RESID, PU>& B, const ProdCursor& c) {
     if (c.b == 0) {
@@ -433,7 +434,7 @@ __device__ void produce_act16(const ConvParams& p, const TcPlan& t, uint8_t* sme
 #pragma unroll
     for (int u = 0; u < PU; ++u) {
       const int e = B.ent[u];
-      const int q = (ptid + (c.b * PU + u) * TC_PROD_THREADS) >> pshift;
+      const int q = (ptid + (c.b * PU + u) * PT) >> pshift;
       if (SIDE) {
         if (e >= 0 && (e & SIDE_BIT)) {
           // the materialised block input is stored as fp16 -- the same rounding the MMA operand gets
@@ -455,20 +456,20 @@ __device__ void produce_act16(const ConvParams& p, const TcPlan& t, uint8_t* sme
   ProdCursor cur;
   cur.tile = first_tile; cur.ch = 0; cur.b = 0; cur.tb = 0u;
   build_table(first_tile, 0u);
-  named_bar_sync(2, TC_PROD_THREADS);
+  named_bar_sync(2, PT);
   ProdBatch<HAS_RESID, PU> B0, B1;
-  prod_load<HAS_RESID, PU>(B0, cur, cur.tile < end_tile, p, t, srcpix, tbl_stride, ptid, pshift, g, nitems);
+  prod_load<HAS_RESID, PU>(B0, cur, cur.tile < end_tile, p, t, srcpix, tbl_stride, ptid, pshift, g, nitems, PT);
   while (cur.tile < end_tile) {
     ProdCursor nxt = cur;
     advance(nxt);
     tile_begin(cur);
-    prod_load<HAS_RESID, PU>(B1, nxt, nxt.tile < end_tile, p, t, srcpix, tbl_stride, ptid, pshift, g, nitems);
+    prod_load<HAS_RESID, PU>(B1, nxt, nxt.tile < end_tile, p, t, srcpix, tbl_stride, ptid, pshift, g, nitems, PT);
     process(B0, cur);
     cur = nxt;
     if (cur.tile >= end_tile) break;
     advance(nxt);
     tile_begin(cur);
-    prod_load<HAS_RESID, PU>(B0, nxt, nxt.tile < end_tile, p, t, srcpix, tbl_stride, ptid, pshift, g, nitems);
+    prod_load<HAS_RESID, PU>(B0, nxt, nxt.tile < end_tile, p, t, srcpix, tbl_stride, ptid, pshift, g, nitems, PT);
     process(B1, cur);
     cur = nxt;
   }
@@ -679,7 +680,7 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
   const int lane = threadIdx.x & 31;
 
   if (threadIdx.x == 0) {
-    for (int s = 0; s < TC_MAX_A_STAGES; ++s) { mbar_init(A_FULL(s), TC_PROD_THREADS); mbar_init(A_EMPTY(s), 1); }
+    for (int s = 0; s < TC_MAX_A_STAGES; ++s) { mbar_init(A_FULL(s), (uint32_t)t.prod_warps * 32u); mbar_init(A_EMPTY(s), 1); }
     for (int s = 0; s < TC_MAX_B_STAGES; ++s) { mbar_init(B_FULL(s), 1); mbar_init(B_EMPTY(s), 1); }
     for (int s = 0; s < 2; ++s) { mbar_init(ACC_FULL(s), 1); mbar_init(ACC_EMPTY(s), 128); }
     fence_barrier_init();
@@ -905,8 +906,9 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
       flush();
       wprof.flush(2, warp == TC_FIRST_EPI_WARP && lane == 0);
     }
-  } else {
+  } else if (warp < TC_FIRST_PROD_WARP + t.prod_warps) {
     // =========================== operand producers ===========================
+    const int PT = t.prod_warps * 32;
     const int ptid = threadIdx.x - TC_FIRST_PROD_WARP * 32;
     const int planes = t.planes;
     const int pshift = planes == 4 ? 2 : (planes == 2 ? 1 : 0);
@@ -946,22 +948,22 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
       constexpr int UB = 8;
       for (int tile = first_tile; tile < end_tile; tile += tile_step) {
         const TileCoord tc = decode_tile(t, tile);
-        named_bar_sync(1, TC_PROD_THREADS);          // every producer is done with the previous tile's tables
+        named_bar_sync(1, PT);          // every producer is done with the previous tile's tables
         if (ptid < t.halo_h) {
           const int sy = map_coord((tc.ty0 + p.oy_off) + ptid - p.pad_t, p.Hc, p.Hs, p.map_mode, p.prepad, p.pad_mode);
           rowv[ptid] = sy < 0 ? -1 : (tc.n * p.Hs + sy) * p.Ws;
         }
-        for (int j = ptid - 64; j >= 0 && j < t.P; j += TC_PROD_THREADS - 64)
+        for (int j = ptid - 64; j >= 0 && j < t.P; j += PT - 64)
           colv[j] = map_coord((tc.tx0 + p.ox_off) + j - p.pad_l, p.Wc, p.Ws, p.map_mode, p.prepad, p.pad_mode);
-        named_bar_sync(2, TC_PROD_THREADS);
+        named_bar_sync(2, PT);
         mbar_wait(A_EMPTY(sa), pa ^ 1u, err, 6);
         uint8_t* plane = smem_a + (size_t)sa * t.a_stage_bytes;
         const uint8_t* __restrict__ src8 = (const uint8_t*)p.src;
-        for (int q0 = ptid; q0 < t.NPOS; q0 += UB * TC_PROD_THREADS) {
+        for (int q0 = ptid; q0 < t.NPOS; q0 += UB * PT) {
           uint32_t raw[UB][2];
 #pragma unroll
           for (int u = 0; u < UB; ++u) {
-            const int q = q0 + u * TC_PROD_THREADS;
+            const int q = q0 + u * PT;
             raw[u][0] = raw[u][1] = 0xFF000000u;                       // top byte set = structural zero
             if (q < t.NPOS) {
               const int hy = (int)(((float)q + 0.5f) * inv_p);
@@ -979,7 +981,7 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
           }
 #pragma unroll
           for (int u = 0; u < UB; ++u) {
-            const int q = q0 + u * TC_PROD_THREADS;
+            const int q = q0 + u * PT;
             if (q >= t.NPOS) continue;
             uint32_t hw[4];
 #pragma unroll
@@ -1003,17 +1005,17 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
     } else
     for (int tile = first_tile; tile < end_tile; tile += tile_step) {
       const TileCoord tc = decode_tile(t, tile);
-      named_bar_sync(1, TC_PROD_THREADS);          // every producer is done with the previous tile's tables
+      named_bar_sync(1, PT);          // every producer is done with the previous tile's tables
       if (nhwc && tc.n != cur_n) {
-        for (int c = ptid; c < p.Cin; c += TC_PROD_THREADS) {
+        for (int c = ptid; c < p.Cin; c += PT) {
           float s_, h_;
           norm_coeff(p, tc.n, c, s_, h_);
           coeff[c] = make_float2(s_, h_);
         }
         cur_n = tc.n;
       }
-      for (int q = ptid; q < t.NPOS; q += TC_PROD_THREADS) srcpix[q] = locate(p, t, tc, q);
-      named_bar_sync(2, TC_PROD_THREADS);
+      for (int q = ptid; q < t.NPOS; q += PT) srcpix[q] = locate(p, t, tc, q);
+      named_bar_sync(2, PT);
       for (int ch = 0; ch < t.nchunks; ++ch) {
         const int c0 = ch * t.CK + g * 8;
         float sc[8], sh[8];
@@ -1026,12 +1028,12 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
         uint8_t* plane_hi = stage + (size_t)g * t.a_plane_bytes;
         uint8_t* plane_lo = plane_hi + t.a_term_bytes;
 
-        for (int idx0 = ptid; idx0 < nitems; idx0 += U * TC_PROD_THREADS) {
+        for (int idx0 = ptid; idx0 < nitems; idx0 += U * PT) {
           int ent[U];
           float x[U][8];
 #pragma unroll
           for (int u = 0; u < U; ++u) {
-            const int idx = idx0 + u * TC_PROD_THREADS;
+            const int idx = idx0 + u * PT;
             ent[u] = idx < nitems ? srcpix[idx >> pshift] : -2;       // -2: nothing to do
           }
           if (nhwc) {
@@ -1075,7 +1077,7 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
               const int npx = t.pair_mode == 2 ? 2 : 1;
               for (int j = 0; j < npx; ++j) {
                 int e = ent[u];
-                if (j == 1) { const int q1 = idx0 + u * TC_PROD_THREADS + 1; e = (ent[u] != -2 && q1 < t.NPOS) ? srcpix[q1] : -1; }
+                if (j == 1) { const int q1 = idx0 + u * PT + 1; e = (ent[u] != -2 && q1 < t.NPOS) ? srcpix[q1] : -1; }
                 if (e < 0) continue;
                 float* xo = &x[u][4 * j];
                 if (p.in_fmt == IN_F32_NCHW3) {
@@ -1098,7 +1100,7 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
 #pragma unroll
           for (int u = 0; u < U; ++u) {
             if (ent[u] == -2) continue;
-            const int q = (idx0 + u * TC_PROD_THREADS) >> pshift;
+            const int q = (idx0 + u * PT) >> pshift;
             uint32_t hi[4];
 #pragma unroll
             for (int i = 0; i < 4; ++i) hi[i] = pack2(x[u][2 * i], x[u][2 * i + 1], is_bf16);

@@ -5,11 +5,11 @@
 namespace nst {
 
 constexpr int TC_MAX_ENT = 81;          // tap entries per channel chunk (9x9 conv)
-constexpr int TC_PROD_WARPS = 8;
+constexpr int TC_PROD_WARPS = 10;        // launched; a layer uses TcPlan::prod_warps (8 or 10) of them
 constexpr int TC_PROD_THREADS = TC_PROD_WARPS * 32;
 constexpr int TC_FIRST_EPI_WARP = 2;
 constexpr int TC_FIRST_PROD_WARP = 6;
-constexpr int TC_THREADS = (TC_FIRST_PROD_WARP + TC_PROD_WARPS) * 32;   // 448
+constexpr int TC_THREADS = (TC_FIRST_PROD_WARP + TC_PROD_WARPS) * 32;   // 512: 16 warps x 128 registers = the whole register file
 constexpr int TC_MAX_A_STAGES = 4;
 constexpr int TC_MAX_B_STAGES = 8;
 constexpr int TC_SMEM_LIMIT = 227 * 1024;
@@ -35,6 +35,7 @@ struct TcPlan {
   int NPAD;                 // UMMA N (Cout padded to a multiple of 16)
   int tg, ngroups;          // entries per weight stage, stages per chunk
   int a_stages, b_stages;
+  int prod_warps;           // operand-producer warps that take part (the rest of TC_PROD_WARPS exit at once)
   int b_resident;           // the layer's whole weight set fits the B ring: load every stage once, never recycle
   int nterms;               // 1, or 3 (hi*hi + lo*hi + hi*lo)
   int a_tplanes, b_tplanes; // operand planes kept (1, or 2 = hi and lo)

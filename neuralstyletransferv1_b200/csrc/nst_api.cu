@@ -259,7 +259,20 @@ static int phase_kind(const LayerSpec& s, int precision) {
   return 0;
 }
 
+// Operand-producer warps per layer.  16 warps x 128 registers fill the register file, so 10 producer warps are free; measured
+// per layer (tools/ab.sh): the producer-bound forms gain 6-10 % with 10 (first layer, stride 2, residual operand, fold_s), the
+// tensor- or epilogue-bound ones lose 3-5 % (more shared-memory traffic against the MMA) and keep 8.
+static int tc_prod_warps(const LayerSpec& s, const TcPlan& t) {
+  if (const char* e = getenv("NST_PROD_WARPS")) { const int v = atoi(e); if (v >= 1 && v <= TC_PROD_WARPS) return v; }
+  return (s.cin == 3 || s.stride == 2 || s.resid >= 0 || t.fold_s) ? TC_PROD_WARPS : 8;
+}
+
+static void tc_plan_static_(const LayerSpec& s, int precision, TcPlan& t);
 static void tc_plan_static(const LayerSpec& s, int precision, TcPlan& t) {
+  tc_plan_static_(s, precision, t);
+  t.prod_warps = tc_prod_warps(s, t);
+}
+static void tc_plan_static_(const LayerSpec& s, int precision, TcPlan& t) {
   memset(&t, 0, sizeof(t));
   if (const int kind = phase_kind(s, precision)) {
     t.phase_mode = kind;

@@ -199,10 +199,11 @@ def test_full_size_1080p_properties():
 
 @pytest.mark.parametrize("arch", ["johnson", "nst", "reconet"])
 @pytest.mark.parametrize("env", [{"NST_NO_PHASE": "1"}, {"NST_NO_FOLD": "1"}, {"NST_NO_QUAD": "1"}, {"NST_NO_SPLIT": "1"},
+                                 {"NST_PROD_WARPS": "8"}, {"NST_PROD_WARPS": "10"}, {"NST_PROD_WARPS": "5"},
                                  {"NST_TC_FORCE": ";".join(f"{i}:3:1" for i in range(16))}])
 def test_kernel_forms_agree(arch, env, monkeypatch):
     """The sub-pixel (phase) form of upsample+conv / ConvTranspose, the folded image layer and any tile shape
-    are re-formulations of the same layer (only the fp32 accumulation order changes): switching them off (or
+    (and the number of operand-producer warps) are re-formulations of the same layer (only the fp32 accumulation order changes): switching them off (or
     forcing 3-row tiles) must leave the uint8 output within the tolerance of itself at PSNR >= 50 dB, and both
     must meet the oracle tolerance."""
     from oracle import nst_oracle as O
