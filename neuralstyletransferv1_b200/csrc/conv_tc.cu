@@ -4,7 +4,7 @@
 // (transformer_net.py:44-54,79-99; transformer_net_nst.py:12-59; model.py:5-15) plus the
 // InstanceNorm/ReLU/residual ops around it (transformer_net.py:30-39,71-76; model.py:30-35,57-60).
 //
-// One persistent CTA per SM, 14 warps, warp-specialised:
+// One persistent CTA per SM, 16 warps (x 128 registers = the whole register file), warp-specialised:
 //   warp 0      weight loader : cp.async.bulk (TMA bulk copy, UBLKCP) of pre-packed fp16 weight
 //                               tiles global -> shared, mbarrier complete_tx ring
 //   warp 1      MMA issuer    : one thread issues tcgen05.mma (M=128, N=Cout, K=16) for every
@@ -13,7 +13,7 @@
 //   warps 2-5   epilogue      : tcgen05.ld TMEM -> registers, store raw fp32 NHWC output,
 //                               per-(n,c) sum / sum-of-squares by warp-shuffle butterfly,
 //                               or bias/tanh/affine/clamp/blend/uint8 pack for the image layer
-//   warps 6-13  operand producers : gather the input halo tile from HBM with reflection /
+//   warps 6-15  operand producers (8 or 10 take part, TcPlan::prod_warps) : gather the input halo tile from HBM with reflection /
 //                               zero padding, nearest-upsample, zero-insertion and stride-2 parity
 //                               split folded into the index math; apply the previous layer's
 //                               InstanceNorm scale/shift + ReLU + residual add in registers;
