@@ -39,9 +39,11 @@ enum nst_arch {
   NST_ARCH_RECONET = 2       /* model.ReCoNet(frn=False)              (model.py:107-116)            */
 };
 
-/* conv operand precision (fp32 accumulate and fp32 activation storage in every mode) */
+/* conv operand precision.  Accumulation is fp32 in every mode.  Raw conv outputs are stored as fp16 in NST_PREC_F16 / BF16
+ * (fp32 between two error-compensated layers) and as fp32 in F16X3 / FP32_DIRECT. */
 enum nst_precision {
-  NST_PREC_F16 = 0,          /* fp16 MMA operands, 1 tcgen05.mma term  (default; meets max|d|<=2, PSNR>=45) */
+  NST_PREC_F16 = 0,          /* fp16 MMA operands, 1 tcgen05.mma term  (default; meets max|d|<=2, PSNR>=45);
+                                ReCoNet's three encoder convs run as F16X3 inside this mode (tanh output is x127.5 steep) */
   NST_PREC_F16X3 = 1,        /* fp16 hi+lo split operands, 3 terms (fp32-class accuracy)              */
   NST_PREC_BF16 = 2,         /* bf16 operands, 1 term (north_star wording; misses the tolerance)      */
   NST_PREC_FP32_DIRECT = 3   /* no tensor cores: fp32 FFMA direct-conv kernels (debug / validation)   */
@@ -83,19 +85,25 @@ int nst_forward_f32_nchw(nst_handle* h, const float* x, float* y, int N, int H, 
                          void* workspace, size_t workspace_bytes, void* stream);
 
 /* Fused uint8 path; replaces ToTensor -> io_preset pre -> model -> io_preset post -> clamp ->
- * [mask composite | uniform blend] -> ToPILImage pack (pipeline.py:1086-1099,1447-1486,
- * 2040-2043,2089-2094; lib.py:27-51).
- *   net_in[c]  = in_scale[c] * u8[src_c] + in_shift[c]     (src_c = 2-c when swap_rb)
- *   out01[c]   = clamp(out_scale[c] * net_out[c'] + out_shift[c], 0, 1)   (c' = 2-c when swap_rb)
- *   if mask:   a = mask[n,h,w]; out01 = clamp(keep ? a*out01+(1-a)*orig : (1-a)*out01+a*orig)
- *   elif 0 <= blend < 1: out01 = clamp(blend*out01 + (1-blend)*orig)       (orig = u8/255)
+ * mask composite -> uniform blend -> ToPILImage pack (pipeline.py:1086-1099,1447-1486,
+ * 2040-2043,2088-2094; lib.py:27-51).
+ *   net_in[c]  = in_scale[c] * u8[src_c] + in_shift[c]                       (src_c = 2-c when swap_rb)
+ *   out01[c]   = clamp((net_out[c'] / out_div[c]) * out_scale[c] + out_shift[c], 0, 1)   (c' = 2-c when swap_rb)
+ *   if mask:            a = mask[n,h,w]; out01 = clamp(keep ? a*out01+(1-a)*orig : (1-a)*out01+a*orig)
+ *   if 0 <= blend < 1:  out01 = clamp(blend*out01 + (1-blend)*orig)          (after the mask composite, pipeline.py:2088-2092;
+ *                                                                             orig = u8/255; any other blend disables)
  *   y_u8 = trunc(out01 * 255)
- * x,y: [dev] uint8 NHWC [N,H,W,3]; requires H,W multiples of 4 (Johnson/ReCoNet) so Ho==H.
+ * Every step after the network is byte work and is evaluated with the reference's own fp32 operation sequence (true division,
+ * separately rounded multiplies and adds; `blend` is a double because Python computes 1.0 - blend in double before torch
+ * narrows it), so y_u8 is bit-identical to the reference's pack of the same fp32 network output.
+ * x: [dev] uint8 NHWC [N,H,W,3]; y: [dev] uint8 NHWC [N,Ho,Wo,3] with (Ho,Wo) = nst_output_shape(H,W) -- equal to (H,W) when
+ * H,W are multiples of 4 (always for NST).  Otherwise the frame comes back Ho x Wo like the reference module's output and the
+ * caller resizes it (pipeline.py:1512-1516, nst_resize_bilinear_u8); mask / blend then require the resize first (NST_ERR_INVALID).
  * mask: [dev] fp32 [N,H,W] or NULL. */
 int nst_forward_u8_nhwc(nst_handle* h, const uint8_t* x, uint8_t* y, int N, int H, int W,
                         const float in_scale[3], const float in_shift[3],
-                        const float out_scale[3], const float out_shift[3], int swap_rb,
-                        float blend, const float* mask, int composite_mode,
+                        const float out_div[3], const float out_scale[3], const float out_shift[3], int swap_rb,
+                        double blend, const float* mask, int composite_mode,
                         void* workspace, size_t workspace_bytes, void* stream);
 
 /* ---- compositing --------------------------------------------------------------------------- */
@@ -121,7 +129,8 @@ int nst_composite_regions_f32(const float* const* srcs, int K, const float* orig
 
 /* Number of conv layers of the model, and per-layer facts of the last plan (after a forward or
  * nst_workspace_bytes): algorithmic FLOPs (2*Ho*Wo*Cout*Cin*k*k*N), algorithmic bytes, and which
- * kernel runs it (0 = direct fp32, 1 = tcgen05).  Arrays are caller-allocated, length >= n. */
+ * kernel runs it (0 = direct fp32, 1 = tcgen05 with per-thread operand gather, 2 = tcgen05 with TMA-fed operands).
+ * Arrays are caller-allocated, length >= n. */
 int nst_num_layers(const nst_handle* h);
 int nst_layer_info(const nst_handle* h, int layer, char* name, int name_cap,
                    double* flops, double* bytes, int* kernel_kind);

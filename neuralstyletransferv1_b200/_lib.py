@@ -29,7 +29,7 @@ PROTOTYPES = {
     "nst_forward_f32_nchw": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int,
                                        C.c_void_p, C.c_size_t, C.c_void_p]),
     "nst_forward_u8_nhwc": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int,
-                                      _c_float3, _c_float3, _c_float3, _c_float3, C.c_int, C.c_float,
+                                      _c_float3, _c_float3, _c_float3, _c_float3, _c_float3, C.c_int, C.c_double,
                                       C.c_void_p, C.c_int, C.c_void_p, C.c_size_t, C.c_void_p]),
     "nst_composite_regions_u8": (C.c_int, [C.POINTER(C.c_void_p), C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int,
                                            C.POINTER(C.c_int), C.POINTER(C.c_float), C.c_void_p, C.c_int, C.c_int,

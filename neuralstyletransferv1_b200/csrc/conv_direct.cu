@@ -18,9 +18,9 @@ constexpr int DIRECT_CO = 16;       // output channels accumulated per pass
 __device__ __forceinline__ float fetch_in(const ConvParams& p, int n, int sy, int sx, int c,
                                           const float2* coeff) {
   if (p.in_fmt == IN_F32_NHWC) {
-    const size_t idx = (((size_t)n * p.Hs + sy) * p.Ws + sx) * p.Cin + c;
+    const size_t idx = act_index(n, c, sy, sx, p.Cin, p.Hs, p.Ws);
     float v = ld_act(p.src, idx, p.act16);
-    if (p.in_stats != nullptr) v = v * coeff[c].x + coeff[c].y;
+    if (p.in_coeff != nullptr) v = v * coeff[c].x + coeff[c].y;
     if (p.pre_relu) v = fmaxf(v, 0.f);
     if (p.resid != nullptr) v += ld_act(p.resid, idx, p.act16);
     if (p.post_relu) v = fmaxf(v, 0.f);
@@ -55,7 +55,7 @@ conv_direct_kernel(const __grid_constant__ ConvParams p, const float* __restrict
   // materialise the transformed input (residual trunk) -- identity-mapped stride-1 layers only
   if (p.side_out != nullptr && valid) {
     for (int c = 0; c < p.Cin; ++c) {
-      st_act(p.side_out, (((size_t)n * p.Hs + oy) * p.Ws + ox) * p.Cin + c, fetch_in(p, n, oy, ox, c, coeff), p.act16);
+      st_act(p.side_out, act_index(n, c, oy, ox, p.Cin, p.Hs, p.Ws), fetch_in(p, n, oy, ox, c, coeff), p.act16);
     }
   }
 
@@ -84,9 +84,8 @@ conv_direct_kernel(const __grid_constant__ ConvParams p, const float* __restrict
     }
     if (p.out_fmt == OUT_F32_NHWC_STATS) {
       if (valid) {
-        const size_t o = (((size_t)n * p.Ho + oy) * p.Wo + ox) * p.Cout + co0;
 #pragma unroll
-        for (int j = 0; j < DIRECT_CO; ++j) if (co0 + j < p.Cout) st_act(p.out, o + j, acc[j], p.act16);
+        for (int j = 0; j < DIRECT_CO; ++j) if (co0 + j < p.Cout) st_act(p.out, act_index(n, co0 + j, oy, ox, p.Cout, p.Ho, p.Wo), acc[j], p.out16);
       }
 #pragma unroll
       for (int j = 0; j < DIRECT_CO; ++j) {
@@ -98,7 +97,7 @@ conv_direct_kernel(const __grid_constant__ ConvParams p, const float* __restrict
           s2 += __shfl_xor_sync(0xffffffffu, s2, off);
         }
         if (lane == 0 && co0 + j < p.Cout) {
-          double* st = p.out_stats + ((size_t)n * p.Cout + co0 + j) * 2;
+          double* st = p.out_part + ((size_t)n * p.Cout + co0 + j) * 2;      // single part, zeroed by the host before the launch
           atomicAdd(st, (double)s1);
           atomicAdd(st + 1, (double)s2);
         }

@@ -82,15 +82,15 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity, unsigne
 // Debug instrumentation (NST_TC_PROF=1): cycles each role spends blocked on each barrier kind.
 struct WaitProf {
   unsigned long long* buf;
-  long long acc[7];
+  long long acc[8];
   long long t_start;
   __device__ __forceinline__ void init(unsigned long long* b) {
     buf = b;
-    if (buf) { for (int i = 0; i < 7; ++i) acc[i] = 0; t_start = clock64(); }
+    if (buf) { for (int i = 0; i < 8; ++i) acc[i] = 0; t_start = clock64(); }
   }
   __device__ __forceinline__ void flush(int role, bool leader) {
     if (buf && leader) {
-      for (int i = 1; i < 7; ++i) if (acc[i]) atomicAdd(buf + i, (unsigned long long)acc[i]);
+      for (int i = 1; i < 8; ++i) if (acc[i]) atomicAdd(buf + i, (unsigned long long)acc[i]);
       atomicAdd(buf + 8 + role, (unsigned long long)(clock64() - t_start));
     }
   }
@@ -125,6 +125,16 @@ __device__ __forceinline__ void bulk_g2s(uint32_t dst_smem, const void* src, uin
   asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                ::"r"(dst_smem), "l"(src), "r"(bytes), "r"(bar)
                : "memory");
+}
+// TMA tiled load of one 4-D box {8 channels, box cols, box rows, 1 plane} of a planar-8 activation tensor
+// (tensor map dims: 8 x W x H x (N * C/8)); out-of-bounds elements arrive as zeros and count towards complete_tx.
+__device__ __forceinline__ void tma_load_4d(uint32_t dst_smem, const CUtensorMap* tmap, int c1, int c2, int c3, uint32_t bar) {
+  asm volatile("cp.async.bulk.tensor.4d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4, %5}], [%6];"
+               ::"r"(dst_smem), "l"(tmap), "r"(0), "r"(c1), "r"(c2), "r"(c3), "r"(bar)
+               : "memory");
+}
+__device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* tmap) {
+  asm volatile("prefetch.tensormap [%0];" ::"l"(tmap) : "memory");
 }
 __device__ __forceinline__ void tmem_alloc(uint32_t dst_smem, uint32_t ncols) {
   asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(dst_smem), "r"(ncols) : "memory");
@@ -209,8 +219,8 @@ __device__ __forceinline__ TileCoord decode_tile(const TcPlan& t, int tile) {
 // ---------------------------------------------------------------------------------------------
 // operand producer: one (halo position, 8-channel group) item
 // ---------------------------------------------------------------------------------------------
-// Source-table entry of one halo slot: -1 = structural zero / filler, else the source pixel index
-// (n*Hs+sy)*Ws+sx (< 2^30), with bit 30 set when this tile owns the materialised ("side") value.
+// Source-table entry of one halo slot: -1 = structural zero / filler, else the in-frame source pixel index
+// sy*Ws+sx (< 2^30), with bit 30 set when this tile owns the materialised ("side") value.
 constexpr int SIDE_BIT = 1 << 30;
 
 __device__ __forceinline__ int locate(const ConvParams& p, const TcPlan& t, const TileCoord& tc, int q) {
@@ -237,7 +247,7 @@ __device__ __forceinline__ int locate(const ConvParams& p, const TcPlan& t, cons
   const int sy = map_coord(uy, p.Hc, p.Hs, p.map_mode, p.prepad, p.pad_mode);
   const int sx = map_coord(ux, p.Wc, p.Ws, p.map_mode, p.prepad, p.pad_mode);
   if (sy < 0 || sx < 0) return -1;
-  int e = (tc.n * p.Hs + sy) * p.Ws + sx;
+  int e = sy * p.Ws + sx;
   if (p.side_out != nullptr) {
     // interior positions of this tile own the materialised value (identity-mapped stride-1 layers)
     const int iy = hy - p.pad_t, ix = hx - p.pad_l;
@@ -327,7 +337,8 @@ __device__ __forceinline__ void prod_load(ProdBatch<HAS_RESID, PU>& B, const Pro
   const __half* __restrict__ src = (const __half*)p.src;
   const __half* __restrict__ res = (const __half*)p.resid;
   const int* tbl = srcpix + c.tb * tbl_stride;
-  const int c0 = c.ch * t.CK + g * 8;
+  // planar-8: slot (n, 8-channel plane, pixel) sits at ((n * Cin/8 + plane) * Hs*Ws + pixel) * 8 elements
+  const size_t plane_base = ((size_t)(c.tile / (t.tiles_x * t.tiles_y)) * (p.Cin >> 3) + (size_t)(c.ch * t.planes + g)) * ((size_t)p.Hs * p.Ws);
 #pragma unroll
   for (int u = 0; u < PU; ++u) {
     const int idx = ptid + (c.b * PU + u) * PT;
@@ -338,7 +349,7 @@ __device__ __forceinline__ void prod_load(ProdBatch<HAS_RESID, PU>& B, const Pro
     B.a[u] = make_uint4(0u, 0u, 0u, 0u);
     if (HAS_RESID) B.r[u] = make_uint4(0u, 0u, 0u, 0u);
     if (B.ent[u] >= 0) {
-      const size_t off = (size_t)(B.ent[u] & (SIDE_BIT - 1)) * p.Cin + c0;
+      const size_t off = (plane_base + (size_t)(B.ent[u] & (SIDE_BIT - 1))) * 8;
       if (!(t.dbg & 1024)) {
       B.a[u] = __ldg(reinterpret_cast<const uint4*>(src + off));
       if (HAS_RESID) B.r[u] = __ldg(reinterpret_cast<const uint4*>(res + off));
@@ -408,7 +419,7 @@ __device__ void produce_act16(const ConvParams& p, const TcPlan& t, uint8_t* sme
       mbar_wait(bar_a_empty0 + 8u * sa, pa ^ 1u, err, 6, wprof);
       plane_hi = smem_a + (size_t)sa * t.a_stage_bytes + (size_t)g * t.a_plane_bytes;
     }
-    const int c0 = c.ch * t.CK + g * 8;
+    const size_t plane_base = ((size_t)(c.tile / (t.tiles_x * t.tiles_y)) * (p.Cin >> 3) + (size_t)(c.ch * t.planes + g)) * ((size_t)p.Hs * p.Ws);
     // straight-line over the PU slots (no per-slot branches, so the PU dependency chains interleave): slots with nothing to do
     // (e == -2) or structural zeros (e == -1) run on zero data and are masked at the store
     uint32_t hi[PU][4];
@@ -441,7 +452,7 @@ __device__ void produce_act16(const ConvParams& p, const TcPlan& t, uint8_t* sme
           uint32_t sv[4];
 #pragma unroll
           for (int i = 0; i < 4; ++i) { if (is_bf16) { const float2 f = unpack2(hi[u][i], 1); sv[i] = pack2(f.x, f.y, 0); } else sv[i] = hi[u][i]; }
-          *reinterpret_cast<uint4*>(side + (size_t)(e & (SIDE_BIT - 1)) * p.Cin + c0) = make_uint4(sv[0], sv[1], sv[2], sv[3]);
+          *reinterpret_cast<uint4*>(side + (plane_base + (size_t)(e & (SIDE_BIT - 1))) * 8) = make_uint4(sv[0], sv[1], sv[2], sv[3]);
         }
       }
       if (e != -2) *reinterpret_cast<uint4*>(plane_hi + (size_t)q * 16) = make_uint4(hi[u][0], hi[u][1], hi[u][2], hi[u][3]);
@@ -472,6 +483,210 @@ __device__ void produce_act16(const ConvParams& p, const TcPlan& t, uint8_t* sme
     prod_load<HAS_RESID, PU>(B0, nxt, nxt.tile < end_tile, p, t, srcpix, tbl_stride, ptid, pshift, g, nitems, PT);
     process(B1, cur);
     cur = nxt;
+  }
+  wprof.flush(3, ptid == 0);
+}
+
+// ---------------------------------------------------------------------------------------------
+// TMA-fed operand path (TcPlan::tma_mode): fp16 planar-8 activations, one MMA term
+// ---------------------------------------------------------------------------------------------
+// The halo tile of a channel chunk reaches shared memory as raw fp16 through cp.async.bulk.tensor -- one box
+// {8 channels, P columns, halo rows} per 8-channel plane, which IS the UMMA K-major core-matrix layout
+// [plane][position][8 x f16] because the planar-8 tensor stores a plane's slots contiguously along W.  Stride-2 layers load
+// the four (row, column) parity sub-planes through four parity views of the source (tensor maps with doubled strides), so
+// filter taps stay unit-stride in the position index.  Out-of-image elements arrive as zeros.  The transform warps then apply
+// the previous layer's InstanceNorm scale/shift + ReLU (+ residual from a second staged tile) in place, shared -> shared, with
+// no index tables and no global gathers; tiles that touch the image border get a second short pass that mirrors (reflection
+// / replicate padding) or zeroes (zero padding) the out-of-image slots from the already transformed in-image ones.
+
+// conv-space coordinate of halo slot (0, 0) of a tile
+__device__ __forceinline__ void tile_origin(const ConvParams& p, const TileCoord& tc, int& u0, int& v0) {
+  u0 = (tc.ty0 + p.oy_off) * p.stride - p.pad_t;
+  v0 = (tc.tx0 + p.ox_off) * p.stride - p.pad_l;
+}
+
+// Loader: one thread walks (tile, channel chunk) in MMA order and keeps the operand ring full.
+__device__ void tma_issue_role(const TcArgs& args, uint8_t* smem_a, uint32_t bar_tma_full0, uint32_t bar_a_empty0, int first_tile, int end_tile) {
+  const ConvParams& p = args.p;
+  const TcPlan& t = args.t;
+  WaitProf wprof; wprof.init(args.prof);
+  const int nmaps = p.stride == 2 ? 4 : 1;
+  for (int i = 0; i < nmaps; ++i) tma_prefetch_desc(&args.tmap[i]);
+  if (p.resid != nullptr) tma_prefetch_desc(&args.tmap_res);
+  const uint32_t box_bytes = (uint32_t)t.tma_rows * (uint32_t)t.P * 16u;
+  const uint32_t stage_tx = box_bytes * (uint32_t)t.planes * (p.stride == 2 ? 4u : 1u) * (p.resid != nullptr ? 2u : 1u);
+  const int c8 = p.Cin >> 3;
+  uint32_t sa = 0, pa = 0;
+  for (int tile = first_tile; tile < end_tile; ++tile) {
+    const TileCoord tc = decode_tile(t, tile);
+    int u0, v0;
+    tile_origin(p, tc, u0, v0);
+    for (int ch = 0; ch < t.nchunks; ++ch) {
+      mbar_wait(bar_a_empty0 + 8u * sa, pa ^ 1u, args.err_flag, 6, wprof);
+      const uint32_t full = bar_tma_full0 + 8u * sa;
+      mbar_arrive_expect_tx(full, stage_tx);
+      const uint32_t stage = smem_u32(smem_a) + sa * t.a_stage_bytes;
+      const int plane0 = tc.n * c8 + ch * t.planes;
+      for (int g = 0; g < t.planes; ++g) {
+        const uint32_t dst = stage + (uint32_t)g * t.a_plane_bytes;
+        if (p.stride == 1) {
+          tma_load_4d(dst, &args.tmap[0], v0, u0, plane0 + g, full);
+          if (p.resid != nullptr) tma_load_4d(dst + t.a_res_off, &args.tmap_res, v0, u0, plane0 + g, full);
+        } else {
+#pragma unroll
+          for (int sub = 0; sub < 4; ++sub) {
+            // halo slot (2i + py, 2j + px) is conv-space (u0 + py + 2i, v0 + px + 2j): row i / column j of the parity view
+            // ((u0 + py) & 1, (v0 + px) & 1) starting at floor((u0 + py) / 2), floor((v0 + px) / 2)  (>> is arithmetic)
+            const int uu = u0 + (sub >> 1), vv = v0 + (sub & 1);
+            tma_load_4d(dst + (uint32_t)(sub * t.SUBPOS) * 16u, &args.tmap[((uu & 1) << 1) | (vv & 1)], vv >> 1, uu >> 1, plane0 + g, full);
+          }
+        }
+      }
+      if (++sa == (uint32_t)t.a_stages) { sa = 0; pa ^= 1u; }
+    }
+  }
+  wprof.flush(4, true);
+}
+
+// halo slot index -> (row, column) inside the halo; false for the filler slots behind a stride-2 parity sub-plane
+__device__ __forceinline__ bool slot_rc(const TcPlan& t, int stride, int q, float inv_p, float inv_sub, int& hy, int& hx) {
+  if (stride == 1) {
+    hy = (int)(((float)q + 0.5f) * inv_p);
+    hx = q - hy * t.P;
+    return true;
+  }
+  const int sub = (int)(((float)q + 0.5f) * inv_sub);
+  const int rem = q - sub * t.SUBPOS;
+  const int i = (int)(((float)rem + 0.5f) * inv_p);
+  const int j = rem - i * t.P;
+  hy = 2 * i + (sub >> 1);
+  hx = 2 * j + (sub & 1);
+  return i < t.tma_rows;
+}
+__device__ __forceinline__ int rc_slot(const TcPlan& t, int stride, int hy, int hx) {
+  if (stride == 1) return hy * t.P + hx;
+  return (((hy & 1) << 1) | (hx & 1)) * t.SUBPOS + (hy >> 1) * t.P + (hx >> 1);
+}
+// padding rule on one conv-space coordinate: the in-image coordinate whose value the out-of-image coordinate u takes, or -1
+// (zero padding; and coordinates of a partial tile so far outside that no produced output reads them)
+__device__ __forceinline__ int pad_donor(int u, int extent, int pad_mode) {
+  if (u >= 0 && u < extent) return u;
+  if (pad_mode == PAD_REFLECT) { const int r = u < 0 ? -u : 2 * (extent - 1) - u; return (r >= 0 && r < extent) ? r : -1; }
+  if (pad_mode == PAD_REPLICATE) return u < 0 ? 0 : extent - 1;
+  return -1;
+}
+
+// MODE / HAS_RESID / SIDE as in produce_act16
+template <bool HAS_RESID, int MODE, bool SIDE>
+__device__ void transform_act16(const TcArgs& args, uint8_t* smem_a, float2* coeff, uint32_t bar_tma_full0, uint32_t bar_a_full0, int first_tile, int end_tile, int ptid) {
+  const ConvParams& p = args.p;
+  const TcPlan& t = args.t;
+  constexpr int PU = 4;
+  const int PT = t.prod_warps * 32;
+  const int planes = t.planes;
+  const int g = (ptid >> 3) & (planes - 1);                 // 8 consecutive lanes sweep one 128-byte core matrix of one plane
+  const int blk0 = ptid / (8 * planes), blk_step = PT / (8 * planes);
+  const int l8 = ptid & 7;
+  const int nblk = (t.npos_used + 7) >> 3;
+  const float lo1 = (p.pre_relu || (!HAS_RESID && p.post_relu)) ? 0.f : -INFINITY;
+  const float lo2 = p.post_relu ? 0.f : -INFINITY;
+  const float inv_p = 1.0f / (float)t.P, inv_sub = p.stride == 2 ? 1.0f / (float)t.SUBPOS : 0.f;
+  const int halo_w = p.stride == 1 ? t.P : t.halo_w;
+  const int per_img = t.tiles_x * t.tiles_y;
+  __half* side = (__half*)p.side_out;
+  WaitProf wprof; wprof.init(args.prof);
+  uint32_t sa = 0, pa = 0;
+  int cur_n = -1;
+  float sc[8], sh[8];
+  for (int tile = first_tile; tile < end_tile; ++tile) {
+    const TileCoord tc = decode_tile(t, tile);
+    int u0, v0;
+    tile_origin(p, tc, u0, v0);
+    if (tc.n != cur_n) {                                      // per-sample InstanceNorm coefficients -> shared table
+      named_bar_sync(1, PT);
+      for (int ch = ptid; ch < p.Cin; ch += PT) {
+        float s_, h_;
+        norm_coeff(p, tc.n, ch, s_, h_);
+        coeff[ch] = make_float2(s_, h_);
+      }
+      cur_n = tc.n;
+      named_bar_sync(2, PT);
+    }
+    const bool border = u0 < 0 || v0 < 0 || u0 + t.halo_h > p.Hc || v0 + halo_w > p.Wc;
+    for (int ch = 0; ch < t.nchunks; ++ch) {
+      {
+        const int c0 = ch * t.CK + g * 8;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) { const float2 cf = coeff[c0 + i]; sc[i] = cf.x; sh[i] = cf.y; }
+      }
+      mbar_wait(bar_tma_full0 + 8u * sa, pa, args.err_flag, 7, wprof);
+      uint8_t* plane = smem_a + (size_t)sa * t.a_stage_bytes + (size_t)g * t.a_plane_bytes;
+      const uint8_t* rplane = plane + t.a_res_off;
+      // side output: slot (hy, hx) of plane (n, ch*planes + g) is source pixel (u0 + hy, v0 + hx) (identity-mapped stride-1 layers)
+      const long long side_base = SIDE ? (((long long)tc.n * (p.Cin >> 3) + (ch * planes + g)) * p.Hs + u0) * p.Ws + v0 : 0;   // in slots; may be < 0
+      for (int blk = blk0; blk < nblk; blk += PU * blk_step) {
+        uint4 a[PU], r[PU];
+#pragma unroll
+        for (int u = 0; u < PU; ++u) {
+          const int q = (blk + u * blk_step) * 8 + l8;
+          const bool live = blk + u * blk_step < nblk;
+          a[u] = live ? *reinterpret_cast<const uint4*>(plane + (size_t)q * 16) : make_uint4(0u, 0u, 0u, 0u);
+          if (HAS_RESID) r[u] = live ? *reinterpret_cast<const uint4*>(rplane + (size_t)q * 16) : make_uint4(0u, 0u, 0u, 0u);
+        }
+#pragma unroll
+        for (int u = 0; u < PU; ++u) {
+          const int q = (blk + u * blk_step) * 8 + l8;
+          const uint32_t aw[4] = {a[u].x, a[u].y, a[u].z, a[u].w};
+          uint32_t rw[4] = {0u, 0u, 0u, 0u};
+          if (HAS_RESID) { rw[0] = r[u].x; rw[1] = r[u].y; rw[2] = r[u].z; rw[3] = r[u].w; }
+          uint32_t hi[4];
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const float2 av = unpack2(aw[i], 0);
+            float x0 = fmaf(av.x, sc[2 * i], sh[2 * i]);
+            float x1 = fmaf(av.y, sc[2 * i + 1], sh[2 * i + 1]);
+            if (MODE == 0) { x0 = fmaxf(x0, lo1); x1 = fmaxf(x1, lo1); }
+            if (HAS_RESID) {
+              const float2 rv = unpack2(rw[i], 0);
+              x0 += rv.x; x1 += rv.y;
+              if (MODE == 0) { x0 = fmaxf(x0, lo2); x1 = fmaxf(x1, lo2); }
+            }
+            hi[i] = MODE == 2 ? pack2_relu(x0, x1, 0) : pack2(x0, x1, 0);
+          }
+          if (blk + u * blk_step < nblk) {
+            *reinterpret_cast<uint4*>(plane + (size_t)q * 16) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+            if (SIDE) {
+              const int hy = (int)(((float)q + 0.5f) * inv_p);
+              const int hx = q - hy * t.P;
+              const int iy = hy - p.pad_t, ix = hx - p.pad_l;
+              if (iy >= 0 && iy < t.TH && ix >= 0 && ix < t.TW && tc.ty0 + iy < p.Ho && tc.tx0 + ix < p.Wo)
+                *reinterpret_cast<uint4*>(side + (size_t)(side_base + (long long)hy * p.Ws + hx) * 8) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+            }
+          }
+        }
+      }
+      if (border) {
+        named_bar_sync(1, PT);                 // every in-image slot of the stage is transformed
+        for (int blk = blk0; blk < nblk; blk += blk_step) {
+          const int q = blk * 8 + l8;
+          int hy, hx;
+          if (!slot_rc(t, p.stride, q, inv_p, inv_sub, hy, hx)) continue;
+          const int u = u0 + hy, v = v0 + hx;
+          if (u >= 0 && u < p.Hc && v >= 0 && v < p.Wc) continue;
+          uint4 val = make_uint4(0u, 0u, 0u, 0u);
+          const int du = pad_donor(u, p.Hc, p.pad_mode), dv = pad_donor(v, p.Wc, p.pad_mode);
+          if (du >= 0 && dv >= 0) {
+            const int dy = du - u0, dx = dv - v0;
+            if (dy < 0 || dy >= t.halo_h || dx < 0 || dx >= halo_w) continue;      // partial-tile overhang: nothing reads this slot
+            val = *reinterpret_cast<const uint4*>(plane + (size_t)rc_slot(t, p.stride, dy, dx) * 16);
+          } else if (p.pad_mode != PAD_ZERO) continue;
+          *reinterpret_cast<uint4*>(plane + (size_t)q * 16) = val;
+        }
+      }
+      fence_proxy_async_smem();       // generic-proxy smem writes -> visible to tcgen05.mma (async proxy)
+      mbar_arrive(bar_a_full0 + 8u * sa);
+      if (++sa == (uint32_t)t.a_stages) { sa = 0; pa ^= 1u; }
+    }
   }
   wprof.flush(3, ptid == 0);
 }
@@ -650,7 +865,7 @@ __device__ __noinline__ void mma_role_phase(const TcPlan& t, const MmaCtx c) {
   wprof.flush(1, (threadIdx.x & 31) == 0);
 }
 
-constexpr int NBARS = 2 * TC_MAX_A_STAGES + 2 * TC_MAX_B_STAGES + 4;
+constexpr int NBARS = 3 * TC_MAX_A_STAGES + 2 * TC_MAX_B_STAGES + 4;     // A_FULL, A_EMPTY, B_FULL, B_EMPTY, ACC_FULL/EMPTY x2, TMA_FULL
 
 __global__ void __launch_bounds__(TC_THREADS, 1)
 conv_tc_kernel(const __grid_constant__ TcArgs args) {
@@ -664,9 +879,9 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem_b + (size_t)t.b_stages * t.b_stage_bytes);
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + NBARS);
   uint32_t* ent_tab = tmem_slot + 4;                                         // [TC_MAX_ENT rounded to 84] tap offsets (MMA warp)
-  int* srcpix = reinterpret_cast<int*>(ent_tab + 84);                       // [NPOS] source table of the current tile
-  float2* coeff = reinterpret_cast<float2*>(srcpix + 2 * ((t.NPOS + 3) & ~3));  // [Cin] InstanceNorm (scale, shift) of sample n (two source tables before it)
-  float* fold_ring = reinterpret_cast<float*>(coeff + 256);                   // [256][TC_FOLD_PITCH] (fold_s layers only)
+  int* srcpix = reinterpret_cast<int*>(ent_tab + 84);                       // [2][NPOS] source tables of the current / next tile (gather producers only)
+  float2* coeff = reinterpret_cast<float2*>(srcpix + t.tbl_ints);             // [Cin] InstanceNorm (scale, shift) of sample n
+  float* fold_ring = reinterpret_cast<float*>(coeff + 256);                   // [256][TC_FOLD_PITCH] (fold_s layers) | double [4 warps][stat_ch][2] statistics
 
   const uint32_t bar0 = smem_u32(bars);
   auto A_FULL = [&](int s) { return bar0 + 8u * (uint32_t)s; };
@@ -675,6 +890,7 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
   auto B_EMPTY = [&](int s) { return bar0 + 8u * (uint32_t)(2 * TC_MAX_A_STAGES + TC_MAX_B_STAGES + s); };
   auto ACC_FULL = [&](int s) { return bar0 + 8u * (uint32_t)(2 * TC_MAX_A_STAGES + 2 * TC_MAX_B_STAGES + s); };
   auto ACC_EMPTY = [&](int s) { return bar0 + 8u * (uint32_t)(2 * TC_MAX_A_STAGES + 2 * TC_MAX_B_STAGES + 2 + s); };
+  auto TMA_FULL = [&](int s) { return bar0 + 8u * (uint32_t)(2 * TC_MAX_A_STAGES + 2 * TC_MAX_B_STAGES + 4 + s); };
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -683,6 +899,7 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
     for (int s = 0; s < TC_MAX_A_STAGES; ++s) { mbar_init(A_FULL(s), (uint32_t)t.prod_warps * 32u); mbar_init(A_EMPTY(s), 1); }
     for (int s = 0; s < TC_MAX_B_STAGES; ++s) { mbar_init(B_FULL(s), 1); mbar_init(B_EMPTY(s), 1); }
     for (int s = 0; s < 2; ++s) { mbar_init(ACC_FULL(s), 1); mbar_init(ACC_EMPTY(s), 128); }
+    for (int s = 0; s < TC_MAX_A_STAGES; ++s) mbar_init(TMA_FULL(s), 1);
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc(smem_u32(tmem_slot), 512);
@@ -794,22 +1011,30 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
       }
       wprof.flush(2, warp == TC_FIRST_EPI_WARP && lane == 0);
     } else {
-      // Per-warp running (sum, sum of squares) of every output channel live in shared memory ([NPAD][2] floats per
-      // warp) so neither loop below needs unrolling; they go to the global double table when the sample changes.
-      float* wstat = fold_ring + (size_t)(warp - TC_FIRST_EPI_WARP) * t.NPAD * 2;
-      for (int c = lane; c < t.NPAD * 2; c += 32) wstat[c] = 0.f;
+      // Per-warp running (sum, sum of squares) of every output channel live in shared memory as DOUBLES ([stat_ch][2] per warp):
+      // a tile contributes fp32 sums over <= MB*128 rows, the running sum over the whole CTA run is double, so E[x^2] - mean^2
+      // stays well conditioned for |mean| >> sigma.  When the sample changes (and at the end) the four warps' sums are added in
+      // a fixed order and written -- no atomics -- to this CTA's slot of the partial table; stats_finalize_kernel folds the CTAs
+      // of a sample in index order, so the statistics (hence the whole forward) are bit-reproducible run to run.
+      double* wstat = reinterpret_cast<double*>(fold_ring) + (size_t)(warp - TC_FIRST_EPI_WARP) * t.stat_ch * 2;
+      for (int c = lane; c < t.stat_ch * 2; c += 32) wstat[c] = 0.0;
       __syncwarp();
       int cur_n = -1;
+      const int etid = threadIdx.x - TC_FIRST_EPI_WARP * 32;
       auto flush = [&]() {
         if (cur_n < 0 || p.out_fmt != OUT_F32_NHWC_STATS) return;
-        __syncwarp();
-        for (int c = lane; c < p.co_pass; c += 32) {
-          double* st = p.out_stats + ((size_t)cur_n * p.Cout + p.co_off + c) * 2;
-          atomicAdd(st, (double)wstat[2 * c]);
-          atomicAdd(st + 1, (double)wstat[2 * c + 1]);
-          wstat[2 * c] = 0.f; wstat[2 * c + 1] = 0.f;
+        named_bar_sync(5, 128);                 // every epilogue warp has added its last tile of sample cur_n
+        double* all = reinterpret_cast<double*>(fold_ring);
+        for (int c = etid; c < p.co_pass; c += 128) {
+          double s1 = 0.0, s2 = 0.0;
+#pragma unroll
+          for (int w = 0; w < 4; ++w) { s1 += all[((size_t)w * t.stat_ch + c) * 2]; s2 += all[((size_t)w * t.stat_ch + c) * 2 + 1]; }
+          double* st = p.out_part + (((size_t)blockIdx.x * p.N + cur_n) * p.Cout + p.co_off + c) * 2;
+          st[0] = s1; st[1] = s2;
+#pragma unroll
+          for (int w = 0; w < 4; ++w) { all[((size_t)w * t.stat_ch + c) * 2] = 0.0; all[((size_t)w * t.stat_ch + c) * 2 + 1] = 0.0; }
         }
-        __syncwarp();
+        named_bar_sync(5, 128);
       };
       const float inv_p = 1.0f / (float)t.P;
       uint32_t it = 0;
@@ -823,8 +1048,11 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
         const uint32_t tbase = tmem_base + ((uint32_t)(quad * 32) << 16) + buf * (uint32_t)(t.MB * t.NPAD);
         if (p.out_fmt == OUT_F32_NHWC_STATS) {
           const int nmb = (t.dbg & 4) ? 0 : t.MB;
-          const int nph = p.phase_mode ? 4 : 1;                             // sub-pixel layers: column = phase*Cout + co
+          const int npair = p.phase_mode ? 2 : 1;                           // sub-pixel layers: column = phase*Cout + co, phase = a*2 + b;
+                                                                            // the two b phases of a row phase a are adjacent pixels
           const int ncg = p.phase_mode ? (p.co_pass >> 4) : njc;               // 16-channel groups of the OUTPUT tensor
+          const int Hout = p.phase_mode ? 2 * p.Ho : p.Ho, Wout = p.phase_mode ? 2 * p.Wo : p.Wo;
+          const size_t plane_elems = (size_t)Hout * Wout * 8;                // one 8-channel plane of the planar-8 output
           for (int cg = 0; cg < ncg; ++cg) {
             // 16 channels at a time: the rows of every M block (and of the four sub-pixel phases, which feed the same
             // channel statistics) are accumulated per lane first, then ONE butterfly (16 -> 8 -> 4 -> 2 -> 1 live
@@ -833,36 +1061,55 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
 #pragma unroll
             for (int i = 0; i < 16; ++i) { s[i] = 0.f; q[i] = 0.f; }
             const int co0 = cg * 16;
-            for (int ph = 0; ph < nph; ++ph) {
-            const int jc = p.phase_mode ? ((ph * p.co_pass) >> 4) + cg : cg;
+            const size_t plane0 = ((size_t)tc.n * (p.Cout >> 3) + (size_t)((p.co_off + co0) >> 3)) * plane_elems;
+            for (int pa = 0; pa < npair; ++pa) {
             for (int mb = 0; mb < nmb; ++mb) {
               const int m = mb * 128 + quad * 32 + lane;
               const int ty = (int)(((float)m + 0.5f) * inv_p);
               const int tx = m - ty * t.P;
               const int oy = tc.ty0 + ty, ox = tc.tx0 + tx;
               const bool valid = ty < t.TH && tx < t.TW && oy < p.Ho && ox < p.Wo;
-              float v[16];
-              tmem_ld16(tbase + (uint32_t)(mb * t.NPAD + jc * 16), v);
+              float v[16], w[16];
+              if (p.phase_mode) {
+                tmem_ld16(tbase + (uint32_t)(mb * t.NPAD + (2 * pa) * p.co_pass + co0), v);          // pixel (2oy+pa, 2ox)
+                tmem_ld16(tbase + (uint32_t)(mb * t.NPAD + (2 * pa + 1) * p.co_pass + co0), w);      // pixel (2oy+pa, 2ox+1)
+              } else {
+                tmem_ld16(tbase + (uint32_t)(mb * t.NPAD + co0), v);
+              }
               if (valid) {
-                size_t oidx;
-                if (p.phase_mode) oidx = (((size_t)tc.n * (2 * p.Ho) + 2 * oy + (ph >> 1)) * (size_t)(2 * p.Wo) + 2 * ox + (ph & 1)) * p.Cout + p.co_off + co0;
-                else oidx = (((size_t)tc.n * p.Ho + oy) * p.Wo + ox) * p.Cout + jc * 16;
-                if (p.act16) {
-                  uint32_t h[8];
+                // planar-8 store: 8 channels of a pixel = one slot; a warp's 32 rows are 32 consecutive pixels of an output row
+                // (phase layers: 64), so each plane receives full 128-byte lines
+                const size_t pix = p.phase_mode ? ((size_t)(2 * oy + pa) * Wout + 2 * ox) : ((size_t)oy * Wout + ox);
+                if (p.out16) {
+                  __half* o = (__half*)p.out + plane0 + pix * 8;
 #pragma unroll
-                  for (int i = 0; i < 8; ++i) h[i] = pack2(v[2 * i], v[2 * i + 1], 0);
-                  uint4* o4 = reinterpret_cast<uint4*>((__half*)p.out + oidx);
-                  o4[0] = make_uint4(h[0], h[1], h[2], h[3]);
-                  o4[1] = make_uint4(h[4], h[5], h[6], h[7]);
+                  for (int hp = 0; hp < 2; ++hp) {                           // the two 8-channel planes of this 16-channel group
+                    uint4* o4 = reinterpret_cast<uint4*>(o + (size_t)hp * plane_elems);
+                    o4[0] = make_uint4(pack2(v[8 * hp], v[8 * hp + 1], 0), pack2(v[8 * hp + 2], v[8 * hp + 3], 0),
+                                       pack2(v[8 * hp + 4], v[8 * hp + 5], 0), pack2(v[8 * hp + 6], v[8 * hp + 7], 0));
+                    if (p.phase_mode)
+                      o4[1] = make_uint4(pack2(w[8 * hp], w[8 * hp + 1], 0), pack2(w[8 * hp + 2], w[8 * hp + 3], 0),
+                                         pack2(w[8 * hp + 4], w[8 * hp + 5], 0), pack2(w[8 * hp + 6], w[8 * hp + 7], 0));
+                  }
                 } else {
-                  float4* o4 = reinterpret_cast<float4*>((float*)p.out + oidx);
-                  o4[0] = make_float4(v[0], v[1], v[2], v[3]);
-                  o4[1] = make_float4(v[4], v[5], v[6], v[7]);
-                  o4[2] = make_float4(v[8], v[9], v[10], v[11]);
-                  o4[3] = make_float4(v[12], v[13], v[14], v[15]);
+                  float* o = (float*)p.out + plane0 + pix * 8;
+#pragma unroll
+                  for (int hp = 0; hp < 2; ++hp) {
+                    float4* o4 = reinterpret_cast<float4*>(o + (size_t)hp * plane_elems);
+                    o4[0] = make_float4(v[8 * hp], v[8 * hp + 1], v[8 * hp + 2], v[8 * hp + 3]);
+                    o4[1] = make_float4(v[8 * hp + 4], v[8 * hp + 5], v[8 * hp + 6], v[8 * hp + 7]);
+                    if (p.phase_mode) {
+                      o4[2] = make_float4(w[8 * hp], w[8 * hp + 1], w[8 * hp + 2], w[8 * hp + 3]);
+                      o4[3] = make_float4(w[8 * hp + 4], w[8 * hp + 5], w[8 * hp + 6], w[8 * hp + 7]);
+                    }
+                  }
                 }
 #pragma unroll
                 for (int i = 0; i < 16; ++i) { s[i] += v[i]; q[i] = fmaf(v[i], v[i], q[i]); }
+                if (p.phase_mode) {
+#pragma unroll
+                  for (int i = 0; i < 16; ++i) { s[i] += w[i]; q[i] = fmaf(w[i], w[i], q[i]); }
+                }
               }
             }
             }
@@ -883,9 +1130,9 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
             const float ts = s[0] + __shfl_xor_sync(0xffffffffu, s[0], 1);
             const float tq = q[0] + __shfl_xor_sync(0xffffffffu, q[0], 1);
             if ((lane & 1) == 0) {
-              float2* w2 = reinterpret_cast<float2*>(wstat) + co0 + my_chan;
-              float2 cur = *w2;
-              cur.x += ts; cur.y += tq;
+              double2* w2 = reinterpret_cast<double2*>(wstat) + co0 + my_chan;
+              double2 cur = *w2;
+              cur.x += (double)ts; cur.y += (double)tq;
               *w2 = cur;
             }
           }
@@ -906,8 +1153,26 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
       flush();
       wprof.flush(2, warp == TC_FIRST_EPI_WARP && lane == 0);
     }
+  } else if (t.tma_mode) {
+    // =========================== TMA-fed operand path ===========================
+    if (warp == TC_FIRST_PROD_WARP + TC_PROD_WARPS - 1) {
+      if (lane == 0) tma_issue_role(args, smem_a, TMA_FULL(0), A_EMPTY(0), first_tile, end_tile);
+    } else if (warp < TC_FIRST_PROD_WARP + t.prod_warps) {
+      const int ptid = threadIdx.x - TC_FIRST_PROD_WARP * 32;
+      const bool has_resid = p.resid != nullptr;
+#define NST_XFORM(R, M) do { if (p.side_out != nullptr) transform_act16<R, M, true>(args, smem_a, coeff, TMA_FULL(0), A_FULL(0), first_tile, end_tile, ptid); \
+                             else transform_act16<R, M, false>(args, smem_a, coeff, TMA_FULL(0), A_FULL(0), first_tile, end_tile, ptid); } while (0)
+      if (has_resid) {
+        if (!p.pre_relu && !p.post_relu) NST_XFORM(true, 1);
+        else if (!p.pre_relu) NST_XFORM(true, 2);
+        else NST_XFORM(true, 0);
+      } else {
+        if (p.pre_relu || p.post_relu) NST_XFORM(false, 2); else NST_XFORM(false, 1);
+      }
+#undef NST_XFORM
+    }
   } else if (warp < TC_FIRST_PROD_WARP + t.prod_warps) {
-    // =========================== operand producers ===========================
+    // =========================== operand producers (per-thread gather) ===========================
     const int PT = t.prod_warps * 32;
     const int ptid = threadIdx.x - TC_FIRST_PROD_WARP * 32;
     const int planes = t.planes;
@@ -1027,6 +1292,7 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
         uint8_t* stage = smem_a + (size_t)sa * t.a_stage_bytes;
         uint8_t* plane_hi = stage + (size_t)g * t.a_plane_bytes;
         uint8_t* plane_lo = plane_hi + t.a_term_bytes;
+        const size_t plane_base = ((size_t)tc.n * (p.Cin >> 3) + (size_t)(ch * planes + g)) * ((size_t)p.Hs * p.Ws);   // planar-8 (nhwc sources)
 
         for (int idx0 = ptid; idx0 < nitems; idx0 += U * PT) {
           int ent[U];
@@ -1042,7 +1308,7 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
             for (int u = 0; u < U; ++u) {
               a[u][0] = a[u][1] = r[u][0] = r[u][1] = make_float4(0.f, 0.f, 0.f, 0.f);
               if (ent[u] >= 0) {
-                const size_t off = (size_t)(ent[u] & (SIDE_BIT - 1)) * p.Cin + c0;
+                const size_t off = (plane_base + (size_t)(ent[u] & (SIDE_BIT - 1))) * 8;
                 const float4* s4 = reinterpret_cast<const float4*>(srcf + off);
                 a[u][0] = __ldg(s4); a[u][1] = __ldg(s4 + 1);
                 if (has_resid) {
@@ -1063,7 +1329,7 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
                 x[u][i] = live ? v : 0.f;
               }
               if (live && (ent[u] & SIDE_BIT)) {
-                float4* d4 = reinterpret_cast<float4*>((float*)p.side_out + (size_t)(ent[u] & (SIDE_BIT - 1)) * p.Cin + c0);
+                float4* d4 = reinterpret_cast<float4*>((float*)p.side_out + (plane_base + (size_t)(ent[u] & (SIDE_BIT - 1))) * 8);
                 d4[0] = make_float4(x[u][0], x[u][1], x[u][2], x[u][3]);
                 d4[1] = make_float4(x[u][4], x[u][5], x[u][6], x[u][7]);
               }
@@ -1081,14 +1347,12 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
                 if (e < 0) continue;
                 float* xo = &x[u][4 * j];
                 if (p.in_fmt == IN_F32_NCHW3) {
-                  // entry = (n*Hs+sy)*Ws+sx  ->  plane-separated address
-                  const int hw = p.Hs * p.Ws;
-                  const int n = e / hw;
-                  const int rem = e - n * hw;
-                  const float* s = srcf + ((size_t)n * 3 * hw + rem);
-                  xo[0] = __ldg(s); xo[1] = __ldg(s + hw); xo[2] = __ldg(s + 2 * (size_t)hw);
+                  // entry = sy*Ws+sx  ->  plane-separated address
+                  const size_t hw = (size_t)p.Hs * p.Ws;
+                  const float* s = srcf + ((size_t)tc.n * 3 * hw + e);
+                  xo[0] = __ldg(s); xo[1] = __ldg(s + hw); xo[2] = __ldg(s + 2 * hw);
                 } else {
-                  const uint8_t* s = (const uint8_t*)p.src + (size_t)e * 3;
+                  const uint8_t* s = (const uint8_t*)p.src + ((size_t)tc.n * p.Hs * p.Ws + e) * 3;
                   const float b0 = (float)__ldg(s), b1 = (float)__ldg(s + 1), b2 = (float)__ldg(s + 2);
                   xo[0] = (p.swap_rb ? b2 : b0) * p.in_scale[0] + p.in_shift[0];
                   xo[1] = b1 * p.in_scale[1] + p.in_shift[1];
@@ -1136,8 +1400,13 @@ cudaError_t conv_tc_init() {
   return cudaFuncSetAttribute(conv_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_LIMIT);
 }
 
+int conv_tc_grid(const TcPlan& t, int num_tiles, int num_sms) {
+  (void)t;
+  return num_tiles < num_sms ? num_tiles : num_sms;
+}
+
 cudaError_t launch_conv_tc(const TcArgs& a, int num_sms, cudaStream_t stream) {
-  const int grid = a.t.num_tiles < num_sms ? a.t.num_tiles : num_sms;
+  const int grid = conv_tc_grid(a.t, a.t.num_tiles, num_sms);
   conv_tc_kernel<<<grid, TC_THREADS, a.t.smem_bytes, stream>>>(a);
   return cudaGetLastError();
 }

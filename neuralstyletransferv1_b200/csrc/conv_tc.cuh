@@ -1,11 +1,13 @@
 // Host/device shared description of the tcgen05 implicit-GEMM conv tiling (see conv_tc.cu).
 #pragma once
+#include <cuda.h>            // CUtensorMap (type only; the encoder is resolved at run time through cudaGetDriverEntryPoint)
 #include "nst_kernels.cuh"
 
 namespace nst {
 
 constexpr int TC_MAX_ENT = 81;          // tap entries per channel chunk (9x9 conv)
-constexpr int TC_PROD_WARPS = 10;        // launched; a layer uses TcPlan::prod_warps (8 or 10) of them
+constexpr int TC_PROD_WARPS = 10;        // launched; a layer uses TcPlan::prod_warps (8 or 10) of them.  TMA-fed layers: at most 9 transform
+                                         // warps, the last launched warp issues the activation TMA boxes
 constexpr int TC_PROD_THREADS = TC_PROD_WARPS * 32;
 constexpr int TC_FIRST_EPI_WARP = 2;
 constexpr int TC_FIRST_PROD_WARP = 6;
@@ -43,6 +45,15 @@ struct TcPlan {
   int fold_s;               // image layer (Cout = 3, k9): GEMM N = (horizontal tap s, co) = 27 of 32 columns, entries = the 9 filter
                             // rows; the epilogue sums T[m + s][s*3 + co] over s through a shared-memory ring (9x fewer MMAs)
   int dbg;                  // debug bits (tools/dbg_sweep.sh): switch pipeline roles off one at a time
+  // TMA-fed operand path (fp16 planar-8 activations, one MMA term): the loader warp copies the raw halo tile of a channel chunk
+  // into the operand stage with cp.async.bulk.tensor (one box per 8-channel plane; four parity boxes per plane on stride-2
+  // layers), the transform warps apply InstanceNorm / ReLU / residual IN PLACE (shared -> shared), then mirror the borders.
+  int tma_mode;
+  int tma_rows;             // box rows: halo_h (stride 1) or TH + 1 (one stride-2 parity sub-plane)
+  int npos_used;            // positions the transform sweeps: halo_h * P (stride 1) or 4 * SUBPOS (stride 2)
+  uint32_t a_res_off;       // byte offset of the residual staging planes inside an operand stage (0 = no residual operand)
+  int tbl_ints;             // ints reserved for the gather producers' two source tables (0 on the TMA-fed path)
+  int stat_ch;              // channels of per-warp statistics scratch (output channels of this launch, rounded up to 16)
   uint32_t a_plane_bytes, a_term_bytes, a_stage_bytes;
   uint32_t b_ent_bytes, b_term_bytes, b_stage_bytes;
   uint32_t smem_bytes;
@@ -55,6 +66,10 @@ struct TcPlan {
 };
 
 struct TcArgs {
+  // tensor maps first: cp.async.bulk.tensor needs them 64-byte aligned in the (constant-bank) kernel parameter space.
+  // [0] source (stride 1) or [py*2+px] the four parity views of the source (stride 2); tmap_res: residual operand.
+  alignas(64) CUtensorMap tmap[4];
+  alignas(64) CUtensorMap tmap_res;
   ConvParams p;
   TcPlan t;
   const void* wpack;        // [chunk][group][term][entry in group][plane][NPAD][8] 16-bit
@@ -63,6 +78,7 @@ struct TcArgs {
 };
 
 cudaError_t launch_conv_tc(const TcArgs& a, int num_sms, cudaStream_t stream);
+int conv_tc_grid(const TcPlan& t, int num_tiles, int num_sms);     // CTAs launched (= parts of the statistics table)
 cudaError_t conv_tc_init();
 
 }  // namespace nst

@@ -109,6 +109,60 @@ __global__ void __launch_bounds__(256) composite_u8x4_kernel(const __grid_consta
   }
 }
 
+// ---------------------------------------------------------------------------------------------
+// InstanceNorm statistics: per-CTA partial (sum, sumsq) -> per-(n, c) (scale, shift) of the consumer layer
+// ---------------------------------------------------------------------------------------------
+// torch.nn.InstanceNorm2d(affine=True) in eval with instance statistics (transformer_net.py:9,66-68; model.py:30-35):
+//   y = (x - mean) / sqrt(var_biased + 1e-5) * gamma + beta  =  x * scale + shift.
+// The conv epilogue leaves one partial per CTA and sample (conv_tc.cu) -- the CTAs whose contiguous tile run intersects sample n
+// are summed here in index order, in double, so the result does not depend on scheduling.  grid_parts == 1: a single part that
+// holds the whole sum (direct kernel).
+struct StatsFinalizeArgs {
+  const double* part;       // [parts][N][C][2]
+  const float* gamma;       // [C]
+  const float* beta;        // [C]
+  float2* coeff;            // [N][C]
+  int parts, N, C;
+  int tiles_per_img;        // tiles of one sample; CTA b owns tiles [b*T/parts, (b+1)*T/parts), T = N * tiles_per_img
+  double inv_count;         // 1 / (H*W)
+};
+
+__global__ void __launch_bounds__(128) stats_finalize_kernel(const __grid_constant__ StatsFinalizeArgs a) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= a.N * a.C) return;
+  const int n = i / a.C, c = i - n * a.C;
+  double s1 = 0.0, s2 = 0.0;
+  if (a.parts == 1) {
+    const double* st = a.part + ((size_t)n * a.C + c) * 2;
+    s1 = st[0]; s2 = st[1];
+  } else {
+    const long long T = (long long)a.N * a.tiles_per_img;
+    const long long lo = (long long)n * a.tiles_per_img, hi = lo + a.tiles_per_img;
+    for (int b = 0; b < a.parts; ++b) {
+      const long long t0 = (long long)b * T / a.parts, t1 = (long long)(b + 1) * T / a.parts;
+      if (t0 >= hi) break;
+      if (t1 <= lo || t0 == t1) continue;
+      const double* st = a.part + (((size_t)b * a.N + n) * a.C + c) * 2;
+      s1 += st[0]; s2 += st[1];
+    }
+  }
+  const double mean = s1 * a.inv_count;
+  double var = s2 * a.inv_count - mean * mean;
+  if (var < 0.0) var = 0.0;
+  const float inv = (float)(1.0 / sqrt(var + (double)kInEps));
+  const float scale = a.gamma[c] * inv;
+  a.coeff[i] = make_float2(scale, a.beta[c] - (float)mean * scale);
+}
+
+cudaError_t launch_stats_finalize(const double* part, int parts, int N, int C, int tiles_per_img, double inv_count,
+                                  const float* gamma, const float* beta, float2* coeff, cudaStream_t stream) {
+  StatsFinalizeArgs a;
+  a.part = part; a.gamma = gamma; a.beta = beta; a.coeff = coeff;
+  a.parts = parts; a.N = N; a.C = C; a.tiles_per_img = tiles_per_img; a.inv_count = inv_count;
+  stats_finalize_kernel<<<(N * C + 127) / 128, 128, 0, stream>>>(a);
+  return cudaGetLastError();
+}
+
 cudaError_t launch_composite(const CompositeArgs& a, bool u8, cudaStream_t stream) {
   if (u8 && ((size_t)a.H * a.W) % 4 == 0) {
     bool aligned = ((uintptr_t)a.out % 4 == 0) && ((uintptr_t)a.masks % 16 == 0) && (a.original == nullptr || (uintptr_t)a.original % 4 == 0);

@@ -29,6 +29,8 @@ struct CompositeArgs {
   float w[COMP_MAX_R * COMP_MAX_J];
 };
 cudaError_t launch_composite(const CompositeArgs& a, bool u8, cudaStream_t stream);
+cudaError_t launch_stats_finalize(const double* part, int parts, int N, int C, int tiles_per_img, double inv_count,
+                                  const float* gamma, const float* beta, float2* coeff, cudaStream_t stream);
 }  // namespace nst
 
 using namespace nst;
@@ -177,18 +179,27 @@ struct LayerDev {
   float* in_beta = nullptr;  // [cin]
   TcPlan tc_static;          // shape-independent part of the tiling
   bool tc_ok = false;
+  int prec = 0;              // NST_PREC_* of THIS layer (a handle in NST_PREC_F16 may run single layers error-compensated, layer_precision())
 };
 
 struct LayerPlan {
   ConvParams p;              // pointers are filled per forward
   TcPlan t;
   bool use_tc = false;
-  int stats_off = 0;         // doubles, per micro-batch frame block
-  int src_stats_layer = -1;
+  int in16 = 0, out16 = 0;   // element type of the activation tensors on the input side (src, resid, side) / of the output
+  int producer = -1;         // layer that wrote `src` (its statistics feed this layer's InstanceNorm), or -1
+  int consumer = -1;         // layer that reads `out` as its source (owns the gamma/beta of the norm in between), or -1
+  size_t part_off = 0;       // bytes from the start of the statistics region: partial table [parts][nb][Cout][2] double
+  size_t coeff_off = 0;      // bytes: [nb][Cout] float2 InstanceNorm (scale, shift) of this layer's output
+  int out_H = 0, out_W = 0;  // extent of the output tensor (full resolution for the sub-pixel layers)
+  int parts = 1;             // slots of the partial table (= SMs for the tcgen05 kernel, 1 for the direct kernel)
   double flops = 0, bytes = 0;
+  // tensor maps of the TMA-fed operand path, encoded for `maps_ws` (re-encoded when the caller's workspace moves)
+  CUtensorMap tmap[4], tmap_res;
+  const void* maps_ws = nullptr;
 };
 
-struct BufDims { int C = 0, H = 0, W = 0; size_t off = 0; size_t elems = 0; };
+struct BufDims { int C = 0, H = 0, W = 0; size_t off = 0; size_t bytes = 0; };   // off / bytes per frame
 
 struct nst_handle {
   int device = 0, arch = 0, precision = 0, num_sms = 148;
@@ -200,9 +211,9 @@ struct nst_handle {
   int out_H = 0, out_W = 0;
   std::vector<LayerPlan> plans;
   BufDims bufs[NBUF];
-  size_t act_floats_per_frame = 0;   // activation ELEMENTS per frame (fp16 or fp32, see act16)
-  int act16 = 0;
-  size_t stats_doubles_per_frame = 0;
+  size_t act_bytes_per_frame = 0;
+  int act16 = 0;                     // default element type of intermediate activations (layers next to an F16X3 layer differ)
+  size_t stats_bytes = 0;            // partial tables + coefficient tables of one micro-batch
   size_t workspace_bytes = 0;
   unsigned int* err_host = nullptr;
   unsigned int* err_dev = nullptr;
@@ -265,6 +276,17 @@ static int phase_kind(const LayerSpec& s, int precision) {
 static int tc_prod_warps(const LayerSpec& s, const TcPlan& t) {
   if (const char* e = getenv("NST_PROD_WARPS")) { const int v = atoi(e); if (v >= 1 && v <= TC_PROD_WARPS) return v; }
   return (s.cin == 3 || s.stride == 2 || s.resid >= 0 || t.fold_s) ? TC_PROD_WARPS : 8;
+}
+
+// Precision of one layer.  A handle in the default NST_PREC_F16 mode runs ReCoNet's three encoder convs error-compensated
+// (fp16 hi+lo operands, three MMA terms, fp32 storage between them): the tanh output is x127.5 steep and the ablation in
+// tools/precision_layers.py puts ~all of the |delta| >= 2 tail of the uint8 output on the rounding of these early layers
+// (n(|d|>=2) 704 -> 4 of 783k values at 272x480; the 4-ppm tail at 3 disappears).  NST_X3_LAYERS=<bitmask> overrides.
+static int layer_precision(int arch, int precision, int li) {
+  if (precision != NST_PREC_F16) return precision;
+  unsigned long long mask = arch == NST_ARCH_RECONET ? 0x7ull : 0ull;
+  if (const char* e = getenv("NST_X3_LAYERS")) mask = strtoull(e, nullptr, 0);
+  return ((mask >> li) & 1ull) ? NST_PREC_F16X3 : NST_PREC_F16;
 }
 
 static void tc_plan_static_(const LayerSpec& s, int precision, TcPlan& t);
@@ -341,6 +363,7 @@ static void tc_plan_static_(const LayerSpec& s, int precision, TcPlan& t) {
 // Lay out one candidate tile (TH x TW outputs, halo pitch P, MB M-blocks) in shared memory; false if it does not fit.
 static bool tc_layout(const ConvParams& p, TcPlan& t, int MB, int bTH, int bTW, int bP) {
   const int e = p.ks - 1;
+  const bool tma = t.tma_mode != 0;
   t.TH = bTH; t.TW = bTW; t.P = bP;
   const int Mused = ceil_div(bTH * bP, 128);
   const int MBu = std::min(MB, std::max(1, Mused));
@@ -362,31 +385,44 @@ static bool tc_layout(const ConvParams& p, TcPlan& t, int MB, int bTH, int bTW, 
       else { for (int r = 0; r < p.ks; ++r) for (int s = 0; s < p.ks; ++s) t.ent_off[k++] = r * bP + s; max_off = e * bP + e; }
     }
     t.NPOS = std::max(MBu * 128 + max_off + 2, t.halo_h * bP + 2);
+    t.tma_rows = t.halo_h; t.npos_used = t.halo_h * bP;
   } else {
     t.halo_h = 2 * bTH + 1; t.halo_w = 2 * bTW + 1;
     t.SUBPOS = (bTH + 1) * bP + 2;
+    if (tma) t.SUBPOS = (int)round_up((size_t)t.SUBPOS, 8);            // every parity sub-plane is a TMA destination: 128-byte aligned
     int k = 0;
     for (int r = 0; r < 3; ++r) for (int s = 0; s < 3; ++s) t.ent_off[k++] = ((r & 1) * 2 + (s & 1)) * t.SUBPOS + (r >> 1) * bP + (s >> 1);
     max_off = 3 * t.SUBPOS + bP + 1;
     t.NPOS = std::max(MBu * 128 + max_off + 2, 4 * t.SUBPOS);
+    t.tma_rows = bTH + 1; t.npos_used = 4 * t.SUBPOS;
   }
-  // plane stride (in 16-byte units) chosen so the producers' 8-lane store phases cover all banks
-  if (t.planes == 4) { while (t.NPOS % 8 != 2) ++t.NPOS; }
+  if (tma) {
+    // TMA destinations (one box per plane) must be 128-byte aligned; the in-place transform touches a plane 128 bytes per
+    // quarter-warp, so any plane stride is bank-conflict free.  Box extents are limited to 256 per dimension.
+    if (bP > 256 || t.tma_rows > 256) return false;
+    t.NPOS = (int)round_up((size_t)t.NPOS, 8);
+  }
+  // plane stride (in 16-byte units) chosen so the gather producers' 8-lane store phases cover all banks
+  else if (t.planes == 4) { while (t.NPOS % 8 != 2) ++t.NPOS; }
   else if (t.planes == 2) { while (t.NPOS % 8 != 4) ++t.NPOS; }
   else { t.NPOS = (int)round_up((size_t)t.NPOS, 2); }
   t.a_plane_bytes = (uint32_t)t.NPOS * 16u;
   t.a_term_bytes = t.a_plane_bytes * (uint32_t)t.planes;
-  t.a_stage_bytes = (uint32_t)round_up((size_t)t.a_term_bytes * t.a_tplanes, 128);
+  t.a_res_off = (tma && p.resid != nullptr) ? t.a_term_bytes : 0u;      // (p.resid is only a flag at plan time)
+  t.a_stage_bytes = (uint32_t)round_up((size_t)t.a_term_bytes * t.a_tplanes + t.a_res_off, 128);
   if (t.a_plane_bytes >= (1u << 18)) return false;
   const int b_total = t.b_stages * (int)t.b_stage_bytes;
-  // barriers + TMEM slot + two per-tile source tables [NPOS] (current / next tile) + per-sample norm coefficients [Cin<=256]
-  // + epilogue scratch: fold ring, or per-warp channel statistics
-  const int bar_bytes = 640 + 2 * (int)round_up((size_t)t.NPOS * 4, 16) + 256 * 8 + (t.fold_s ? TC_FOLD_RING_BYTES : 4 * t.NPAD * 8);
+  // barriers + TMEM slot + entry table (704) + the gather producers' two per-tile source tables [NPOS] (current / next tile)
+  // + per-sample norm coefficients [Cin<=256] + epilogue scratch: fold ring, or per-warp double channel statistics
+  t.tbl_ints = tma ? 0 : 2 * (int)round_up((size_t)t.NPOS, 4);
+  t.stat_ch = (int)round_up((size_t)(t.phase_mode ? t.NPAD / 4 : t.NPAD), 16);
+  const int bar_bytes = 704 + t.tbl_ints * 4 + 256 * 8 + (t.fold_s ? TC_FOLD_RING_BYTES : 4 * t.stat_ch * 16);
   const int avail = TC_SMEM_LIMIT - b_total - bar_bytes;
   const int a_stages = avail / (int)t.a_stage_bytes;
   const int want = t.nchunks == 1 ? 2 : 3;
   if (a_stages < 2 && MB > 1) return false;
   if (a_stages < 1) return false;
+  if (tma && a_stages < 2) return false;                                 // the loader must be able to run a stage ahead of the transform
   t.a_stages = std::min(a_stages, std::min(TC_MAX_A_STAGES, want + 1));
   t.MB = MBu;
   t.tiles_x = ceil_div(p.Wo, t.TW);
@@ -425,7 +461,10 @@ static bool tc_plan_geometry(const ConvParams& p, TcPlan& t, int force_TH = 0, i
       const double tiles = (double)cand.tiles_x * cand.tiles_y;
       // short halo rows gather worse (tools/tile_sweep.py: wide, flat tiles win by 3-7 % at equal position count)
       const double row_factor = p.stride == 1 ? 1.0 + 8.0 / cand.P : 1.0;
-      const double prod_cyc = (double)cand.NPOS * cand.planes * cand.nchunks * 3.4 * row_factor;
+      // operand cost per 16-byte slot: ~3.4 SM cycles for the gather producers; the TMA-fed in-place transform has no
+      // table / address work and no row-length sensitivity (estimate, re-fit from profiles/r02_tcprof_*)
+      const double prod_cyc = cand.tma_mode ? (double)cand.npos_used * cand.planes * cand.nchunks * (p.resid ? 1.6 : 1.2)
+                                            : (double)cand.NPOS * cand.planes * cand.nchunks * 3.4 * row_factor;
       const double cost = tiles * (std::max(mma_cyc, prod_cyc) + 0.25 * std::min(mma_cyc, prod_cyc) + 1500.0);
       if (cost < best) { best = cost; best_plan = cand; found = true; }
     }
@@ -516,7 +555,7 @@ static std::vector<uint16_t> tc_pack_weights(const LayerSpec& s, const TcPlan& t
 // lifetime
 // ---------------------------------------------------------------------------------------------
 extern "C" const char* nst_last_error(void) { return g_err; }
-extern "C" const char* nst_version(void) { return "b200nst 0.1 (sm_100a, tcgen05 implicit-GEMM conv)"; }
+extern "C" const char* nst_version(void) { return "b200nst 0.2 (sm_100a, tcgen05 implicit-GEMM conv, TMA-fed operands)"; }
 
 extern "C" int nst_create(int device, int arch, int precision, nst_handle** out) {
   if (out == nullptr) return fail(NST_ERR_INVALID, "nst_create: out is null");
@@ -537,6 +576,7 @@ extern "C" int nst_create(int device, int arch, int precision, nst_handle** out)
   h->num_sms = prop.multiProcessorCount;
   h->specs = arch == NST_ARCH_JOHNSON ? johnson_layers() : (arch == NST_ARCH_NST ? nst_layers() : reconet_layers());
   h->dev.resize(h->specs.size());
+  for (size_t li = 0; li < h->specs.size(); ++li) h->dev[li].prec = layer_precision(arch, precision, (int)li);
   if (const char* mbs = getenv("NST_MICROBATCH")) h->microbatch = std::max(1, atoi(mbs));
   if (const char* d = getenv("NST_TC_DBG")) h->dbg = atoi(d);
   if (const char* d = getenv("NST_TC_LAYER_MASK")) h->tc_layer_mask = strtoull(d, nullptr, 0);
@@ -553,7 +593,22 @@ extern "C" int nst_create(int device, int arch, int precision, nst_handle** out)
 
 static void free_layer(LayerDev& d) {
   cudaFree(d.wdir); cudaFree(d.wpack); cudaFree(d.wpack2); cudaFree(d.bias); cudaFree(d.in_gamma); cudaFree(d.in_beta);
+  const int prec = d.prec;
   d = LayerDev();
+  d.prec = prec;
+}
+
+// static (shape-independent) tcgen05 form of a layer: whether it has one, whether it runs as two channel halves, its tiling constants
+static void layer_static_plan(const LayerSpec& s, LayerDev& d) {
+  d.tc_ok = d.prec != NST_PREC_FP32_DIRECT && tc_supported(s);
+  d.nsplit = 1;
+  if (!d.tc_ok) return;
+  // a sub-pixel layer whose 4*Cout accumulator columns do not fit TMEM (ReCoNet decoder.layers.1: 4*96) runs as two
+  // launches over half of the output channels each
+  LayerSpec half = s;
+  half.cout = s.cout / 2;
+  d.nsplit = (4 * s.cout > 256 && s.cout % 32 == 0 && phase_kind(half, d.prec) != 0 && !getenv("NST_NO_SPLIT")) ? 2 : 1;
+  tc_plan_static(d.nsplit == 2 ? half : s, d.prec, d.tc_static);
 }
 
 extern "C" void nst_destroy(nst_handle* h) {
@@ -575,6 +630,7 @@ static cudaError_t upload(T** dst, const std::vector<T>& src) {
 extern "C" int nst_load_weights(nst_handle* h, int n_tensors, const char* const* names, const float* const* ptrs,
                                 const int64_t* shapes, int* n_missing, int* n_unexpected) {
   if (h == nullptr) return fail(NST_ERR_INVALID, "nst_load_weights: null handle");
+  if (n_tensors < 0 || (n_tensors > 0 && (!names || !ptrs || !shapes))) return fail(NST_ERR_INVALID, "nst_load_weights: null argument");
   CUDA_TRY(cudaSetDevice(h->device));
   struct T { const float* p; int64_t s[4]; };
   std::map<std::string, T> m;
@@ -583,29 +639,54 @@ extern "C" int nst_load_weights(nst_handle* h, int n_tensors, const char* const*
     for (int k = 0; k < 4; ++k) t.s[k] = shapes[i * 4 + k];
     m[names[i]] = t;
   }
+  // ---- pass 1: validate every tensor (names, shapes) before anything on the handle is touched ----
   std::map<std::string, bool> used;
   int missing = 0;
-  auto get = [&](const std::string& key, int64_t s0, int64_t s1, int64_t s2, int64_t s3, std::vector<float>& dst) -> int {
+  std::string first_problem;
+  auto want = [&](const std::string& key, int64_t s0, int64_t s1, int64_t s2, int64_t s3) {
     auto it = m.find(key);
-    if (it == m.end()) { ++missing; return fail(NST_ERR_WEIGHTS, "nst_load_weights: missing tensor '%s'", key.c_str()); }
+    char msg[384];
+    if (it == m.end() || it->second.p == nullptr) {
+      ++missing;
+      if (first_problem.empty()) { snprintf(msg, sizeof(msg), "missing tensor '%s'", key.c_str()); first_problem = msg; }
+      return;
+    }
     const T& t = it->second;
-    if (t.s[0] != s0 || t.s[1] != s1 || t.s[2] != s2 || t.s[3] != s3)
-      return fail(NST_ERR_WEIGHTS, "nst_load_weights: '%s' has shape [%lld,%lld,%lld,%lld], expected [%lld,%lld,%lld,%lld]", key.c_str(),
-                  (long long)t.s[0], (long long)t.s[1], (long long)t.s[2], (long long)t.s[3], (long long)s0, (long long)s1, (long long)s2, (long long)s3);
     used[key] = true;
-    dst.assign(t.p, t.p + (size_t)(s0 * s1 * s2 * s3));
-    return NST_OK;
+    if ((t.s[0] != s0 || t.s[1] != s1 || t.s[2] != s2 || t.s[3] != s3) && first_problem.empty()) {
+      snprintf(msg, sizeof(msg), "'%s' has shape [%lld,%lld,%lld,%lld], expected [%lld,%lld,%lld,%lld]", key.c_str(), (long long)t.s[0],
+               (long long)t.s[1], (long long)t.s[2], (long long)t.s[3], (long long)s0, (long long)s1, (long long)s2, (long long)s3);
+      first_problem = msg;
+    }
+  };
+  for (const LayerSpec& s : h->specs) {
+    if (s.transposed) want(s.wkey, s.cin, s.cout, s.ks, s.ks); else want(s.wkey, s.cout, s.cin, s.ks, s.ks);
+    want(s.bkey, s.cout, 1, 1, 1);
+    if (!s.in_gkey.empty()) { want(s.in_gkey, s.cin, 1, 1, 1); want(s.in_bkey, s.cin, 1, 1, 1); }
+  }
+  int unexpected = 0;
+  for (auto& kv : m) if (!used.count(kv.first)) ++unexpected;
+  if (n_missing) *n_missing = missing;
+  if (n_unexpected) *n_unexpected = unexpected;
+  if (!first_problem.empty())
+    return fail(NST_ERR_WEIGHTS, "nst_load_weights: %s (%d missing, %d unexpected); the handle keeps its previous weights", first_problem.c_str(), missing, unexpected);
+  // ---- pass 2: repack and upload into fresh buffers; the handle switches over only when every layer succeeded ----
+  auto get = [&](const std::string& key, std::vector<float>& dst) {
+    const T& t = m[key];
+    dst.assign(t.p, t.p + (size_t)(t.s[0] * t.s[1] * t.s[2] * t.s[3]));
+  };
+  std::vector<LayerDev> fresh(h->specs.size());
+  auto abandon = [&](cudaError_t e, const char* what) {
+    for (auto& d : fresh) free_layer(d);
+    return fail(NST_ERR_CUDA, "nst_load_weights: %s: %s; the handle keeps its previous weights", what, cudaGetErrorString(e));
   };
   for (size_t li = 0; li < h->specs.size(); ++li) {
     const LayerSpec& s = h->specs[li];
-    LayerDev& d = h->dev[li];
-    free_layer(d);
+    LayerDev& d = fresh[li];
+    d.prec = h->dev[li].prec;
     std::vector<float> w_raw, w, bias, gam, bet;
-    int rc;
-    if (s.transposed) rc = get(s.wkey, s.cin, s.cout, s.ks, s.ks, w_raw);
-    else rc = get(s.wkey, s.cout, s.cin, s.ks, s.ks, w_raw);
-    if (rc != NST_OK) return rc;
-    if ((rc = get(s.bkey, s.cout, 1, 1, 1, bias)) != NST_OK) return rc;
+    get(s.wkey, w_raw);
+    get(s.bkey, bias);
     // canonical OIHW of the equivalent direct convolution
     w.resize((size_t)s.cout * s.cin * s.ks * s.ks);
     if (s.transposed) {
@@ -619,38 +700,32 @@ extern "C" int nst_load_weights(nst_handle* h, int n_tensors, const char* const*
     std::vector<float> wdir((size_t)s.ks * s.ks * s.cin * s.cout);
     for (int co = 0; co < s.cout; ++co) for (int ci = 0; ci < s.cin; ++ci) for (int r = 0; r < s.ks; ++r) for (int q = 0; q < s.ks; ++q)
       wdir[((size_t)(r * s.ks + q) * s.cin + ci) * s.cout + co] = w[(((size_t)co * s.cin + ci) * s.ks + r) * s.ks + q];
-    CUDA_TRY(upload(&d.wdir, wdir));
-    CUDA_TRY(upload(&d.bias, bias));
+    cudaError_t e;
+    if ((e = upload(&d.wdir, wdir)) != cudaSuccess) return abandon(e, "upload weights");
+    if ((e = upload(&d.bias, bias)) != cudaSuccess) return abandon(e, "upload bias");
     if (!s.in_gkey.empty()) {
-      if ((rc = get(s.in_gkey, s.cin, 1, 1, 1, gam)) != NST_OK) return rc;
-      if ((rc = get(s.in_bkey, s.cin, 1, 1, 1, bet)) != NST_OK) return rc;
-      CUDA_TRY(upload(&d.in_gamma, gam));
-      CUDA_TRY(upload(&d.in_beta, bet));
+      get(s.in_gkey, gam); get(s.in_bkey, bet);
+      if ((e = upload(&d.in_gamma, gam)) != cudaSuccess) return abandon(e, "upload gamma");
+      if ((e = upload(&d.in_beta, bet)) != cudaSuccess) return abandon(e, "upload beta");
     }
-    d.tc_ok = h->precision != NST_PREC_FP32_DIRECT && tc_supported(s);
+    layer_static_plan(s, d);
     if (d.tc_ok) {
-      // a sub-pixel layer whose 4*Cout accumulator columns do not fit TMEM (ReCoNet decoder.layers.1: 4*96) runs as two
-      // launches over half of the output channels each
-      LayerSpec half = s;
-      half.cout = s.cout / 2;
-      d.nsplit = (4 * s.cout > 256 && s.cout % 32 == 0 && phase_kind(half, h->precision) != 0 && !getenv("NST_NO_SPLIT")) ? 2 : 1;
-      const LayerSpec& ps = d.nsplit == 2 ? half : s;
-      tc_plan_static(ps, h->precision, d.tc_static);
+      LayerSpec ps = s;
+      ps.cout = s.cout / d.nsplit;
       d.tc_static.dbg = h->dbg;
       for (int part = 0; part < d.nsplit; ++part) {
         std::vector<float> wpart(w.begin() + (size_t)part * ps.cout * s.cin * s.ks * s.ks, w.begin() + (size_t)(part + 1) * ps.cout * s.cin * s.ks * s.ks);
         std::vector<uint16_t> pk = tc_pack_weights(ps, d.tc_static, wpart);
-        CUDA_TRY(upload((uint16_t**)(part == 0 ? &d.wpack : &d.wpack2), pk));
+        if ((e = upload((uint16_t**)(part == 0 ? &d.wpack : &d.wpack2), pk)) != cudaSuccess) return abandon(e, "upload packed weights");
       }
     }
   }
-  int unexpected = 0;
-  for (auto& kv : m) if (!used.count(kv.first)) ++unexpected;
-  if (n_missing) *n_missing = missing;
-  if (n_unexpected) *n_unexpected = unexpected;
-  CUDA_TRY(cudaDeviceSynchronize());
+  cudaError_t e = cudaDeviceSynchronize();
+  if (e != cudaSuccess) return abandon(e, "synchronize");
+  for (size_t li = 0; li < h->specs.size(); ++li) { free_layer(h->dev[li]); h->dev[li] = fresh[li]; }
   h->weights_loaded = true;
   h->plan_N = 0;
+  h->plans.clear();
   return NST_OK;
 }
 
@@ -669,6 +744,17 @@ extern "C" int nst_output_shape(const nst_handle* h, int H, int W, int* Ho, int*
   return NST_OK;
 }
 
+// A layer takes the TMA-fed operand path when its source is an fp16 planar-8 activation tensor that the conv reads through the
+// identity map (the sub-pixel forms of the up-sampling layers are identity-mapped over the low-res tensor), with one MMA term.
+static bool tma_eligible(const ConvParams& q, const TcPlan& t, int in16) {
+  if (getenv("NST_NO_TMA")) return false;
+  if (!in16 || t.nterms != 1 || t.pair_mode || t.is_bf16 || t.a_tplanes != 1) return false;
+  if (q.map_mode != MAP_IDENTITY || (q.stride != 1 && q.stride != 2)) return false;
+  if (q.stride == 2 && (q.Hs < 2 || q.Ws < 2)) return false;
+  if (q.Cin % 8 != 0) return false;
+  return true;
+}
+
 static int make_plan(nst_handle* h, int N, int H, int W) {
   if (N < 1 || H < 1 || W < 1) return fail(NST_ERR_INVALID, "bad shape N=%d H=%d W=%d", N, H, W);
   if (h->arch == NST_ARCH_NST && (H <= 40 || W <= 40))
@@ -677,10 +763,30 @@ static int make_plan(nst_handle* h, int N, int H, int W) {
     return fail(NST_ERR_INVALID, "input %dx%d too small for ReflectionPad2d(4)", H, W);
   if (h->plan_N == N && h->plan_H == H && h->plan_W == W && !h->plans.empty()) return NST_OK;
   const int nb = std::min(N, h->microbatch);
+  const int nl = (int)h->specs.size();
   h->plans.assign(h->specs.size(), LayerPlan());
   for (int b = 0; b < NBUF; ++b) h->bufs[b] = BufDims();
   int producer[NBUF];
   for (int b = 0; b < NBUF; ++b) producer[b] = -1;
+  // who reads what: producer / consumer links and the element type of every activation tensor.  An error-compensated (F16X3)
+  // layer stores fp32 only when its consumer is error-compensated too, so plain fp16 layers always read fp16.
+  for (int li = 0; li < nl; ++li) {
+    const LayerSpec& s = h->specs[li];
+    LayerPlan& lp = h->plans[li];
+    if (s.src != BUF_IMAGE) {
+      lp.producer = producer[s.src];
+      if (lp.producer < 0) return fail(NST_ERR_STATE, "internal: layer %s reads an unwritten buffer", s.name.c_str());
+      h->plans[lp.producer].consumer = li;
+    }
+    if (s.out != BUF_IMAGE) producer[s.out] = li;
+  }
+  for (int li = 0; li < nl; ++li) {
+    LayerPlan& lp = h->plans[li];
+    const bool x3 = h->dev[li].prec == NST_PREC_F16X3;
+    const bool cons_x3 = lp.consumer >= 0 && h->dev[lp.consumer].prec == NST_PREC_F16X3;
+    lp.out16 = h->act16 && !(x3 && cons_x3);
+    if (h->precision == NST_PREC_F16X3 || h->precision == NST_PREC_FP32_DIRECT) lp.out16 = h->act16;
+  }
   size_t stats_off = 0;
   for (size_t li = 0; li < h->specs.size(); ++li) {
     const LayerSpec& s = h->specs[li];
@@ -692,16 +798,17 @@ static int make_plan(nst_handle* h, int N, int H, int W) {
     p.pad_t = p.pad_l = s.pad;
     p.pre_relu = s.pre_relu; p.post_relu = s.post_relu; p.tanh_out = s.tanh_out;
     p.blend = 1.f;
-    p.act16 = h->act16;
     p.co_off = 0; p.co_pass = s.cout / h->dev[li].nsplit;
+    lp.in16 = s.src == BUF_IMAGE ? h->act16 : h->plans[lp.producer].out16;
+    if ((s.resid >= 0 || s.side >= 0) && lp.in16 != h->act16)
+      return fail(NST_ERR_STATE, "internal: layer %s mixes fp32 source with fp16 residual tensors", s.name.c_str());
+    p.act16 = lp.in16; p.out16 = lp.out16;
     if (s.src == BUF_IMAGE) { p.Hs = H; p.Ws = W; }
     else {
       const BufDims& bd = h->bufs[s.src];
       if (bd.C != s.cin) return fail(NST_ERR_STATE, "internal: layer %s expects %d channels, buffer has %d", s.name.c_str(), s.cin, bd.C);
       p.Hs = bd.H; p.Ws = bd.W;
-      lp.src_stats_layer = producer[s.src];
     }
-    p.in_inv_count = 1.0f / ((float)p.Hs * (float)p.Ws);
     switch (s.map_mode) {
       case MAP_UP2: case MAP_ZERO_INSERT2: p.Hc = 2 * p.Hs; p.Wc = 2 * p.Ws; break;
       case MAP_PREPAD_REFLECT: p.Hc = p.Hs + 80; p.Wc = p.Ws + 80; break;
@@ -723,22 +830,20 @@ static int make_plan(nst_handle* h, int N, int H, int W) {
     } else {
       BufDims& bd = h->bufs[s.out];
       bd.C = s.cout; bd.H = p.Ho; bd.W = p.Wo;
-      bd.elems = std::max(bd.elems, (size_t)s.cout * p.Ho * p.Wo);
-      producer[s.out] = (int)li;
-      lp.stats_off = (int)stats_off;
-      stats_off += (size_t)s.cout * 2;
+      lp.out_H = p.Ho; lp.out_W = p.Wo;
+      bd.bytes = std::max(bd.bytes, (size_t)s.cout * p.Ho * p.Wo * (lp.out16 ? 2 : 4));
     }
     if (s.side >= 0) {
       BufDims& bd = h->bufs[s.side];
       bd.C = s.cin; bd.H = p.Hs; bd.W = p.Ws;
-      bd.elems = std::max(bd.elems, (size_t)s.cin * p.Hs * p.Ws);
+      bd.bytes = std::max(bd.bytes, (size_t)s.cin * p.Hs * p.Ws * (lp.in16 ? 2 : 4));
     }
     lp.flops = 2.0 * p.Ho * p.Wo * (double)s.cout * s.cin * s.ks * s.ks;      // per frame
     {   // algorithmic HBM bytes per frame: each operand once, image tensors at their own element size
-      const double esz = h->act16 ? 2.0 : 4.0;
-      const double in_b = s.src == BUF_IMAGE ? 3.0 * p.Hs * p.Ws : esz * p.Hs * p.Ws * s.cin;
-      const double out_b = s.out == BUF_IMAGE ? 3.0 * p.Ho * p.Wo : esz * p.Ho * p.Wo * s.cout;
-      lp.bytes = in_b + out_b + esz * (double)p.Hs * p.Ws * s.cin * ((s.resid >= 0 ? 1 : 0) + (s.side >= 0 ? 1 : 0));
+      const double in_esz = lp.in16 ? 2.0 : 4.0, out_esz = lp.out16 ? 2.0 : 4.0;
+      const double in_b = s.src == BUF_IMAGE ? 3.0 * p.Hs * p.Ws : in_esz * p.Hs * p.Ws * s.cin;
+      const double out_b = s.out == BUF_IMAGE ? 3.0 * p.Ho * p.Wo : out_esz * p.Ho * p.Wo * s.cout;
+      lp.bytes = in_b + out_b + in_esz * (double)p.Hs * p.Ws * s.cin * ((s.resid >= 0 ? 1 : 0) + (s.side >= 0 ? 1 : 0));
     }
     lp.use_tc = h->dev[li].tc_ok && ((h->tc_layer_mask >> li) & 1ull);
     int fTH = 0, fMB = 0;
@@ -751,23 +856,46 @@ static int make_plan(nst_handle* h, int N, int H, int W) {
     }
     if (lp.use_tc) {
       lp.t = h->dev[li].tc_static;
+      ConvParams q = p;
       if (lp.t.phase_mode) {
         // tile over the low-res grid; the epilogue scatters the four phases into the [N, 2Hs, 2Ws, Cout] output
-        ConvParams q = p;
         q.phase_mode = lp.t.phase_mode; q.map_mode = MAP_IDENTITY; q.pad_mode = lp.t.phase_mode == 1 ? PAD_REPLICATE : PAD_ZERO;
         q.Hc = p.Hs; q.Wc = p.Ws; q.Ho = p.Hs; q.Wo = p.Ws;
-        if (tc_plan_geometry(q, lp.t, fTH, fMB)) p = q; else lp.use_tc = false;
-      } else if (!tc_plan_geometry(p, lp.t, fTH, fMB)) lp.use_tc = false;
+      }
+      q.resid = s.resid >= 0 ? (const void*)1 : nullptr;                   // plan-time flag (operand stage holds a residual tile too)
+      lp.t.tma_mode = tma_eligible(q, lp.t, lp.in16) ? 1 : 0;
+      if (lp.t.tma_mode) lp.t.prod_warps = std::min(lp.t.prod_warps, TC_PROD_WARPS - 1);
+      bool ok = tc_plan_geometry(q, lp.t, fTH, fMB);
+      if (!ok && lp.t.tma_mode) {                                            // shapes the TMA boxes cannot express fall back to the gather producers
+        lp.t = h->dev[li].tc_static;
+        ok = tc_plan_geometry(q, lp.t, fTH, fMB);
+      }
+      q.resid = nullptr;
+      if (!ok)
+        return fail(NST_ERR_INVALID, "layer %s (%d->%d k%d s%d, %dx%d): no tcgen05 tiling fits; only NST_PREC_FP32_DIRECT runs this shape",
+                    s.name.c_str(), s.cin, s.cout, s.ks, s.stride, p.Hs, p.Ws);
+      p = q;
+    } else if (h->precision != NST_PREC_FP32_DIRECT && ((h->tc_layer_mask >> li) & 1ull)) {
+      // never degrade silently to the fp32 FFMA kernel (~50x slower): the caller asked for a tensor-core precision
+      return fail(NST_ERR_INVALID, "layer %s (%d->%d k%d s%d) has no tcgen05 form; only NST_PREC_FP32_DIRECT runs it", s.name.c_str(), s.cin,
+                  s.cout, s.ks, s.stride);
+    }
+    if (s.out != BUF_IMAGE) {
+      lp.parts = lp.use_tc ? h->num_sms : 1;
+      lp.part_off = stats_off;
+      stats_off += round_up((size_t)lp.parts * nb * s.cout * 2 * sizeof(double), 256);
+      lp.coeff_off = stats_off;
+      stats_off += round_up((size_t)nb * s.cout * sizeof(float2), 256);
     }
   }
   size_t off = 0;
   for (int b = 0; b < NBUF; ++b) {
     h->bufs[b].off = off;
-    off += round_up(h->bufs[b].elems, 64);
+    off += round_up(h->bufs[b].bytes, 256);
   }
-  h->act_floats_per_frame = off;
-  h->stats_doubles_per_frame = stats_off;
-  h->workspace_bytes = round_up(off * (h->act16 ? 2 : 4) * nb, 256) + round_up(stats_off * sizeof(double) * nb, 256) + 256;
+  h->act_bytes_per_frame = off;
+  h->stats_bytes = stats_off;
+  h->workspace_bytes = round_up(off * nb, 256) + round_up(stats_off, 256) + 256;
   h->plan_N = N; h->plan_H = H; h->plan_W = W; h->plan_nb = nb;
   return NST_OK;
 }
@@ -787,9 +915,60 @@ extern "C" int nst_workspace_bytes(nst_handle* h, int N, int H, int W, size_t* b
 struct IoSpec {
   int in_fmt, out_fmt;
   const void* x; void* y;
-  float in_scale[3], in_shift[3], out_scale[3], out_shift[3];
-  int swap_rb; float blend; const float* mask; int composite_mode;
+  float in_scale[3], in_shift[3], out_div[3], out_scale[3], out_shift[3];
+  int swap_rb; double blend; const float* mask; int composite_mode;
 };
+
+// cuTensorMapEncodeTiled through the runtime's driver-entry-point lookup (libcuda is not linked)
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn encode_tiled_fn() {
+  static EncodeTiledFn fn = nullptr;
+  if (fn == nullptr) {
+    void* ptr = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &qres) == cudaSuccess && qres == cudaDriverEntryPointSuccess)
+      fn = (EncodeTiledFn)ptr;
+  }
+  return fn;
+}
+
+// Tensor map over a view of a planar-8 fp16 activation tensor: dims {8 channels, W, H, N*C/8 planes}; box {8, box_w, box_h, 1}.
+// `sx` / `sy` = 2 selects every second column / row starting at `base` (the parity views of the stride-2 layers).
+static int encode_act_map(CUtensorMap* m, const void* base, int W, int H, size_t planes, int sx, int sy, size_t row_bytes, size_t plane_bytes,
+                          int box_w, int box_h) {
+  EncodeTiledFn fn = encode_tiled_fn();
+  if (fn == nullptr) return fail(NST_ERR_CUDA, "cuTensorMapEncodeTiled is not available from this driver");
+  const cuuint64_t dims[4] = {8, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)planes};
+  const cuuint64_t strides[3] = {(cuuint64_t)(16 * sx), (cuuint64_t)(row_bytes * sy), (cuuint64_t)plane_bytes};
+  const cuuint32_t box[4] = {8, (cuuint32_t)box_w, (cuuint32_t)box_h, 1};
+  const cuuint32_t estr[4] = {1, 1, 1, 1};
+  const CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 4, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                        CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS)
+    return fail(NST_ERR_CUDA, "cuTensorMapEncodeTiled failed (%d) for view %dx%d planes=%zu strides=%d/%zu/%zu box=%dx%d", (int)r, W, H, planes,
+                16 * sx, row_bytes * sy, plane_bytes, box_w, box_h);
+  return NST_OK;
+}
+
+static int encode_layer_maps(LayerPlan& lp, const ConvParams& p, const void* src, const void* resid, int nb) {
+  const TcPlan& t = lp.t;
+  const size_t planes = (size_t)nb * (p.Cin >> 3);
+  const size_t row_bytes = (size_t)p.Ws * 16, plane_bytes = (size_t)p.Hs * p.Ws * 16;
+  int rc;
+  if (p.stride == 1) {
+    if ((rc = encode_act_map(&lp.tmap[0], src, p.Ws, p.Hs, planes, 1, 1, row_bytes, plane_bytes, t.P, t.tma_rows)) != NST_OK) return rc;
+    if (resid != nullptr && (rc = encode_act_map(&lp.tmap_res, resid, p.Ws, p.Hs, planes, 1, 1, row_bytes, plane_bytes, t.P, t.tma_rows)) != NST_OK) return rc;
+  } else {
+    for (int py = 0; py < 2; ++py) for (int px = 0; px < 2; ++px) {
+      const char* base = (const char*)src + ((size_t)py * p.Ws + px) * 16;
+      rc = encode_act_map(&lp.tmap[py * 2 + px], base, (p.Ws - px + 1) / 2, (p.Hs - py + 1) / 2, planes, 2, 2, row_bytes, plane_bytes, t.P, t.tma_rows);
+      if (rc != NST_OK) return rc;
+    }
+  }
+  return NST_OK;
+}
 
 static int run_forward(nst_handle* h, const IoSpec& io, int N, int H, int W, void* workspace, size_t workspace_bytes,
                        cudaStream_t stream, float* layer_ms) {
@@ -804,22 +983,21 @@ static int run_forward(nst_handle* h, const IoSpec& io, int N, int H, int W, voi
   if (((uintptr_t)workspace & 255) != 0) return fail(NST_ERR_INVALID, "forward: workspace must be 256-byte aligned");
   if (*h->err_host != 0) return fail(NST_ERR_CUDA, "forward: a previous kernel reported pipeline error 0x%08x", *h->err_host);
   const int nb = h->plan_nb;
-  const size_t esz = h->act16 ? 2 : 4;
   char* act = (char*)workspace;
-  double* stats = (double*)((char*)workspace + round_up(h->act_floats_per_frame * esz * nb, 256));
-  const size_t stats_bytes = h->stats_doubles_per_frame * sizeof(double) * nb;
+  char* stats = (char*)workspace + round_up(h->act_bytes_per_frame * nb, 256);
   const int Ho = h->out_H, Wo = h->out_W;
   const size_t in_px = (size_t)H * W * 3, out_px = (size_t)Ho * Wo * 3;
   const size_t in_elt = io.in_fmt == IN_U8_NHWC3 ? 1 : 4, out_elt = io.out_fmt == OUT_U8_NHWC3 ? 1 : 4;
+  const bool blend_on = io.blend >= 0.0 && io.blend < 1.0;                 // pipeline.py:2089
   std::vector<cudaEvent_t> ev;
   if (layer_ms) {
     ev.resize(h->specs.size() + 1);
     for (auto& e : ev) CUDA_TRY(cudaEventCreate(&e));
     for (size_t i = 0; i < h->specs.size(); ++i) layer_ms[i] = 0.f;
   }
+  auto buf = [&](int b) -> void* { return act + h->bufs[b].off * nb; };
   for (int n0 = 0; n0 < N; n0 += nb) {
     const int n = std::min(nb, N - n0);
-    CUDA_TRY(cudaMemsetAsync(stats, 0, stats_bytes, stream));
     if (layer_ms) CUDA_TRY(cudaEventRecord(ev[0], stream));
     for (size_t li = 0; li < h->specs.size(); ++li) {
       const LayerSpec& s = h->specs[li];
@@ -827,7 +1005,6 @@ static int run_forward(nst_handle* h, const IoSpec& io, int N, int H, int W, voi
       LayerPlan& lp = h->plans[li];
       ConvParams p = lp.p;
       p.N = n;
-      auto buf = [&](int b) -> void* { return act + h->bufs[b].off * nb * esz; };
       if (s.src == BUF_IMAGE) {
         p.in_fmt = io.in_fmt;
         p.src = (const char*)io.x + (size_t)n0 * in_px * in_elt;
@@ -836,8 +1013,7 @@ static int run_forward(nst_handle* h, const IoSpec& io, int N, int H, int W, voi
       } else {
         p.in_fmt = IN_F32_NHWC;
         p.src = buf(s.src);
-        p.in_stats = stats + (size_t)h->plans[lp.src_stats_layer].stats_off * nb;
-        p.in_gamma = d.in_gamma; p.in_beta = d.in_beta;
+        p.in_coeff = (const float2*)(stats + h->plans[lp.producer].coeff_off);
       }
       p.resid = s.resid >= 0 ? buf(s.resid) : nullptr;
       p.side_out = s.side >= 0 ? buf(s.side) : nullptr;
@@ -845,22 +1021,37 @@ static int run_forward(nst_handle* h, const IoSpec& io, int N, int H, int W, voi
       if (s.out == BUF_IMAGE) {
         p.out_fmt = io.out_fmt;
         p.out = (char*)io.y + (size_t)n0 * out_px * out_elt;
-        for (int c = 0; c < 3; ++c) { p.out_scale[c] = io.out_scale[c]; p.out_shift[c] = io.out_shift[c]; }
+        for (int c = 0; c < 3; ++c) { p.out_div[c] = io.out_div[c]; p.out_scale[c] = io.out_scale[c]; p.out_shift[c] = io.out_shift[c]; }
         p.swap_rb = io.swap_rb;
-        p.blend = io.blend; p.composite_mode = io.composite_mode;
+        // Python evaluates `blend * S + (1.0 - blend) * O` with double scalars that torch then narrows to fp32 (pipeline.py:2090)
+        p.blend = blend_on ? (float)io.blend : 2.f;
+        p.blend_comp = (float)(1.0 - io.blend);
+        p.composite_mode = io.composite_mode;
         p.mask = io.mask ? io.mask + (size_t)n0 * Ho * Wo : nullptr;
-        p.orig = (io.in_fmt == IN_U8_NHWC3 && (io.mask != nullptr || io.blend < 1.f)) ? (const uint8_t*)io.x + (size_t)n0 * in_px : nullptr;
+        p.orig = (io.in_fmt == IN_U8_NHWC3 && (io.mask != nullptr || blend_on)) ? (const uint8_t*)io.x + (size_t)n0 * in_px : nullptr;
       } else {
         p.out_fmt = OUT_F32_NHWC_STATS;
         p.out = buf(s.out);
-        p.out_stats = stats + (size_t)lp.stats_off * nb;
+        p.out_part = (double*)(stats + lp.part_off);
       }
-      // per-layer statistics tables are [nb][C][2]: stats_off counts doubles per frame
+      int parts = 1, tiles_per_img = 0;
       if (lp.use_tc) {
         TcArgs a;
         a.p = p; a.t = lp.t;
         a.t.num_tiles = lp.t.tiles_x * lp.t.tiles_y * n;
         a.err_flag = h->err_dev;
+        if (lp.t.tma_mode) {
+          if (lp.maps_ws != workspace) {
+            if ((rc = encode_layer_maps(lp, p, p.src, p.resid, nb)) != NST_OK) return rc;
+            lp.maps_ws = workspace;
+          }
+          memcpy(a.tmap, lp.tmap, sizeof(a.tmap));
+          a.tmap_res = lp.tmap_res;
+        } else {
+          memset(a.tmap, 0, sizeof(a.tmap)); memset(&a.tmap_res, 0, sizeof(a.tmap_res));
+        }
+        parts = conv_tc_grid(a.t, a.t.num_tiles, h->num_sms);
+        tiles_per_img = lp.t.tiles_x * lp.t.tiles_y;
         for (int part = 0; part < d.nsplit; ++part) {
         a.wpack = part == 0 ? d.wpack : d.wpack2;
         a.p.co_off = part * a.p.co_pass;
@@ -874,15 +1065,25 @@ static int run_forward(nst_handle* h, const IoSpec& io, int N, int H, int W, voi
           CUDA_TRY(cudaMemcpyAsync(pc, a.prof, sizeof(pc), cudaMemcpyDeviceToHost, stream));
           CUDA_TRY(cudaStreamSynchronize(stream));
           const double g = std::min(a.t.num_tiles, h->num_sms);
-          fprintf(stderr, "[tcprof] %-12s tiles=%d ctas=%.0f | per-CTA kcycles: loader total %.0f wait B_EMPTY %.0f | mma total %.0f wait ACC_EMPTY %.0f A_FULL %.0f B_FULL %.0f | "
-                          "epi total %.0f wait ACC_FULL %.0f | prod total %.0f wait A_EMPTY %.0f\n", s.name.c_str(), a.t.num_tiles, g,
+          fprintf(stderr, "[tcprof] %-12s %s tiles=%d ctas=%.0f | per-CTA kcycles: loader total %.0f wait B_EMPTY %.0f | mma total %.0f wait ACC_EMPTY %.0f A_FULL %.0f B_FULL %.0f | "
+                          "epi total %.0f wait ACC_FULL %.0f | prod total %.0f wait A_EMPTY %.0f | tma-issue total %.0f, transform waits TMA_FULL %.0f\n", s.name.c_str(),
+                  lp.t.tma_mode ? "tma" : "gather", a.t.num_tiles, g,
                   pc[8] / g / 1e3, pc[1] / g / 1e3, pc[9] / g / 1e3, pc[2] / g / 1e3, pc[3] / g / 1e3, pc[4] / g / 1e3, pc[10] / g / 1e3, pc[5] / g / 1e3,
-                  pc[11] / g / 1e3, pc[6] / g / 1e3);
+                  pc[11] / g / 1e3, pc[6] / g / 1e3, pc[12] / g / 1e3, pc[7] / g / 1e3);
         }
       } else {
+        if (s.out != BUF_IMAGE) CUDA_TRY(cudaMemsetAsync(p.out_part, 0, (size_t)n * s.cout * 2 * sizeof(double), stream));
         CUDA_TRY(launch_conv_direct(p, d.wdir, stream));
       }
       ++h->launches;
+      if (s.out != BUF_IMAGE) {
+        // fold the per-CTA partial statistics into the (scale, shift) the consumer applies (its gamma / beta belong to the norm in between)
+        if (lp.consumer < 0) return fail(NST_ERR_STATE, "internal: layer %s has no consumer", s.name.c_str());
+        const LayerDev& cd = h->dev[lp.consumer];
+        CUDA_TRY(launch_stats_finalize(p.out_part, parts, n, s.cout, tiles_per_img, 1.0 / ((double)lp.out_H * lp.out_W), cd.in_gamma, cd.in_beta,
+                                       (float2*)(stats + lp.coeff_off), stream));
+        ++h->launches;
+      }
       if (layer_ms) CUDA_TRY(cudaEventRecord(ev[li + 1], stream));
     }
     if (layer_ms) {
@@ -903,35 +1104,40 @@ extern "C" int nst_forward_f32_nchw(nst_handle* h, const float* x, float* y, int
   IoSpec io;
   memset(&io, 0, sizeof(io));
   io.in_fmt = IN_F32_NCHW3; io.out_fmt = OUT_F32_NCHW3; io.x = x; io.y = y;
-  for (int c = 0; c < 3; ++c) { io.in_scale[c] = 1.f; io.out_scale[c] = 1.f; }
-  io.blend = 1.f;
+  for (int c = 0; c < 3; ++c) { io.in_scale[c] = 1.f; io.out_div[c] = 1.f; io.out_scale[c] = 1.f; }
+  io.blend = 1.0;
   return run_forward(h, io, N, H, W, workspace, workspace_bytes, (cudaStream_t)stream, nullptr);
 }
 
 static int fill_u8_io(nst_handle* h, IoSpec& io, const uint8_t* x, uint8_t* y, int H, int W, const float in_scale[3],
-                      const float in_shift[3], const float out_scale[3], const float out_shift[3], int swap_rb, float blend,
-                      const float* mask, int composite_mode) {
+                      const float in_shift[3], const float out_div[3], const float out_scale[3], const float out_shift[3], int swap_rb,
+                      double blend, const float* mask, int composite_mode) {
   if (h == nullptr) return fail(NST_ERR_INVALID, "forward_u8: null handle");
-  if (!in_scale || !in_shift || !out_scale || !out_shift) return fail(NST_ERR_INVALID, "forward_u8: null affine");
+  if (!in_scale || !in_shift || !out_div || !out_scale || !out_shift) return fail(NST_ERR_INVALID, "forward_u8: null affine");
+  for (int c = 0; c < 3; ++c) if (out_div[c] == 0.f) return fail(NST_ERR_INVALID, "forward_u8: out_div[%d] is zero", c);
   int Ho, Wo;
   out_shape(h->arch, H, W, &Ho, &Wo);
-  if (Ho != H || Wo != W) return fail(NST_ERR_INVALID, "forward_u8: H,W must be multiples of 4 for this architecture (got %dx%d -> %dx%d)", H, W, Ho, Wo);
+  // H or W not a multiple of 4: the stride-2 convs round up, the output is the larger Ho x Wo frame (nst_output_shape) exactly like
+  // the reference module's; the caller resizes it back (pipeline.py:1512-1516, frame_pipeline.py).  Blending with the H x W original
+  // is only defined after that resize.
+  if ((Ho != H || Wo != W) && (mask != nullptr || (blend >= 0.0 && blend < 1.0)))
+    return fail(NST_ERR_INVALID, "forward_u8: blend / mask need H,W multiples of 4 for this architecture (got %dx%d -> %dx%d); resize first", H, W, Ho, Wo);
   memset(&io, 0, sizeof(io));
   io.in_fmt = IN_U8_NHWC3; io.out_fmt = OUT_U8_NHWC3; io.x = x; io.y = y;
   for (int c = 0; c < 3; ++c) {
     io.in_scale[c] = in_scale[c]; io.in_shift[c] = in_shift[c];
-    io.out_scale[c] = out_scale[c]; io.out_shift[c] = out_shift[c];
+    io.out_div[c] = out_div[c]; io.out_scale[c] = out_scale[c]; io.out_shift[c] = out_shift[c];
   }
   io.swap_rb = swap_rb; io.blend = blend; io.mask = mask; io.composite_mode = composite_mode;
   return NST_OK;
 }
 
 extern "C" int nst_forward_u8_nhwc(nst_handle* h, const uint8_t* x, uint8_t* y, int N, int H, int W, const float in_scale[3],
-                                   const float in_shift[3], const float out_scale[3], const float out_shift[3], int swap_rb,
-                                   float blend, const float* mask, int composite_mode, void* workspace, size_t workspace_bytes,
-                                   void* stream) {
+                                   const float in_shift[3], const float out_div[3], const float out_scale[3], const float out_shift[3],
+                                   int swap_rb, double blend, const float* mask, int composite_mode, void* workspace,
+                                   size_t workspace_bytes, void* stream) {
   IoSpec io;
-  int rc = fill_u8_io(h, io, x, y, H, W, in_scale, in_shift, out_scale, out_shift, swap_rb, blend, mask, composite_mode);
+  int rc = fill_u8_io(h, io, x, y, H, W, in_scale, in_shift, out_div, out_scale, out_shift, swap_rb, blend, mask, composite_mode);
   if (rc != NST_OK) return rc;
   return run_forward(h, io, N, H, W, workspace, workspace_bytes, (cudaStream_t)stream, nullptr);
 }
@@ -939,9 +1145,9 @@ extern "C" int nst_forward_u8_nhwc(nst_handle* h, const uint8_t* x, uint8_t* y, 
 extern "C" int nst_profile_layers_u8(nst_handle* h, const uint8_t* x, uint8_t* y, int N, int H, int W, void* workspace,
                                      size_t workspace_bytes, void* stream, float* ms) {
   if (ms == nullptr) return fail(NST_ERR_INVALID, "nst_profile_layers_u8: ms is null");
-  const float one[3] = {1.f, 1.f, 1.f}, zero[3] = {0.f, 0.f, 0.f}, inv[3] = {1.f / 255.f, 1.f / 255.f, 1.f / 255.f};
+  const float one[3] = {1.f, 1.f, 1.f}, zero[3] = {0.f, 0.f, 0.f}, d255[3] = {255.f, 255.f, 255.f};
   IoSpec io;
-  int rc = fill_u8_io(h, io, x, y, H, W, one, zero, inv, zero, 0, 1.f, nullptr, 0);
+  int rc = fill_u8_io(h, io, x, y, H, W, one, zero, d255, one, zero, 0, 1.0, nullptr, 0);
   if (rc != NST_OK) return rc;
   return run_forward(h, io, N, H, W, workspace, workspace_bytes, (cudaStream_t)stream, ms);
 }
@@ -957,7 +1163,7 @@ extern "C" int nst_layer_info(const nst_handle* h, int layer, char* name, int na
   if (name && name_cap > 0) { strncpy(name, h->specs[layer].name.c_str(), name_cap - 1); name[name_cap - 1] = 0; }
   if (flops) *flops = h->plans[layer].flops;
   if (bytes) *bytes = h->plans[layer].bytes;
-  if (kernel_kind) *kernel_kind = h->plans[layer].use_tc ? 1 : 0;
+  if (kernel_kind) *kernel_kind = h->plans[layer].use_tc ? (h->plans[layer].t.tma_mode ? 2 : 1) : 0;
   return NST_OK;
 }
 
@@ -1008,8 +1214,8 @@ extern "C" int nst_describe_plan(int arch, int precision, int N, int H, int W, c
   h.dev.resize(h.specs.size());
   if (const char* mbs = getenv("NST_MICROBATCH")) h.microbatch = std::max(1, atoi(mbs));
   for (size_t li = 0; li < h.specs.size(); ++li) {
-    h.dev[li].tc_ok = precision != NST_PREC_FP32_DIRECT && tc_supported(h.specs[li]);
-    if (h.dev[li].tc_ok) tc_plan_static(h.specs[li], precision, h.dev[li].tc_static);
+    h.dev[li].prec = layer_precision(arch, precision, (int)li);
+    layer_static_plan(h.specs[li], h.dev[li]);
   }
   int rc = make_plan(&h, N, H, W);
   if (rc != NST_OK) return rc;
@@ -1025,9 +1231,10 @@ extern "C" int nst_describe_plan(int arch, int precision, int N, int H, int W, c
     if (lp.use_tc) {
       const double useful = (double)lp.p.Ho * lp.p.Wo / ((double)t.tiles_x * t.tiles_y * t.MB * 128);
       snprintf(line, sizeof(line),
-               "%-28s %3d->%3d k%d s%d %4dx%-4d -> %4dx%-4d tc  TH=%2d TW=%3d P=%3d MB=%d NPOS=%4d CK=%2d chunks=%d ent=%2d tg=%d "
+               "%-28s %3d->%3d k%d s%d %4dx%-4d -> %4dx%-4d tc %s%s TH=%2d TW=%3d P=%3d MB=%d NPOS=%4d CK=%2d chunks=%d ent=%2d tg=%d "
                "A=%dx%uB B=%dx%uB smem=%uB tiles/img=%d rows_useful=%.2f GF=%.2f\n",
-               sp.name.c_str(), sp.cin, sp.cout, sp.ks, sp.stride, lp.p.Hs, lp.p.Ws, lp.p.Ho, lp.p.Wo, t.TH, t.TW, t.P, t.MB, t.NPOS,
+               sp.name.c_str(), sp.cin, sp.cout, sp.ks, sp.stride, lp.p.Hs, lp.p.Ws, lp.p.Ho, lp.p.Wo, t.tma_mode ? "tma   " : "gather",
+               h.dev[li].prec == NST_PREC_F16X3 ? " x3" : (lp.out16 ? "" : " f32"), t.TH, t.TW, t.P, t.MB, t.NPOS,
                t.CK, t.nchunks, t.nent, t.tg, t.a_stages, t.a_stage_bytes, t.b_stages, t.b_stage_bytes, t.smem_bytes,
                t.tiles_x * t.tiles_y, useful, lp.flops * 1e-9);
     } else {

@@ -18,29 +18,32 @@ CAFFE_MEAN = (103.939, 116.779, 123.68)   # pipeline.py:1465
 
 
 def io_preset_affine(preset: str):
-    """uint8 -> network input and network output -> out01 as per-channel affines.
+    """uint8 -> network input and network output -> out01, per channel.
 
-    Folds ToTensor (/255, pipeline.py:1099) and the io_preset branches of
-    pipeline.py:1447-1486 into ``in = s_in*u8 + b_in`` and ``out01 = s_out*y + b_out``
-    (+ R/B swap for caffe_bgr).  Returns (in_scale, in_shift, out_scale, out_shift, swap_rb).
+    Folds ToTensor (/255, pipeline.py:1099) and the io_preset branches of pipeline.py:1447-1486 into
+    ``in = s_in*u8 + b_in`` and ``out01 = clamp((y / d_out) * s_out + b_out, 0, 1)`` (+ R/B swap for
+    caffe_bgr).  The output side keeps the reference's own operation per preset -- a true division for
+    the ``/255`` presets, multiply-then-add for ``imagenet_01`` / ``tanh`` -- because the uint8 pack that
+    follows truncates and must be bit-identical.  Returns
+    (in_scale, in_shift, out_div, out_scale, out_shift, swap_rb).  An unknown preset takes the
+    reference's final ``else`` branch (pipeline.py:1482-1486), i.e. raw_255.
     """
     one, zero = (1.0, 1.0, 1.0), (0.0, 0.0, 0.0)
+    d255 = (255.0,) * 3
     inv255 = (1.0 / 255.0,) * 3
-    if preset == "raw_255":
-        return one, zero, inv255, zero, 0
     if preset == "raw_01":
-        return inv255, zero, one, zero, 0
+        return inv255, zero, one, one, zero, 0
     if preset == "tanh":
-        return (2.0 / 255.0,) * 3, (-1.0,) * 3, (0.5,) * 3, (0.5,) * 3, 0
+        return (2.0 / 255.0,) * 3, (-1.0,) * 3, one, (0.5,) * 3, (0.5,) * 3, 0      # (y + 1) * 0.5 == y * 0.5 + 0.5 exactly in fp32
     if preset in ("imagenet_01", "imagenet_255"):
         s_in = tuple(1.0 / (255.0 * s) for s in IMAGENET_STD)
         b_in = tuple(-m / s for m, s in zip(IMAGENET_MEAN, IMAGENET_STD))
         if preset == "imagenet_01":
-            return s_in, b_in, IMAGENET_STD, IMAGENET_MEAN, 0
-        return s_in, b_in, inv255, zero, 0
+            return s_in, b_in, one, IMAGENET_STD, IMAGENET_MEAN, 0
+        return s_in, b_in, d255, one, zero, 0
     if preset == "caffe_bgr":
-        return one, tuple(-m for m in CAFFE_MEAN), inv255, zero, 1
-    raise ValueError(f"unknown io_preset {preset!r}")
+        return one, tuple(-m for m in CAFFE_MEAN), d255, one, zero, 1
+    return one, zero, d255, one, zero, 0          # raw_255 and the reference's default branch
 
 
 def _f3(v: Sequence[float]):
@@ -145,20 +148,27 @@ class Engine:
     def stylize_u8(self, frames: torch.Tensor, preset: str, blend: float = 1.0,
                    mask: Optional[torch.Tensor] = None, composite_mode: str = "keep",
                    out: Optional[torch.Tensor] = None) -> torch.Tensor:
-        """uint8 NHWC frames -> stylised uint8 NHWC (whole per-frame path of pipeline.py, fused)."""
+        """uint8 NHWC frames -> stylised uint8 NHWC (whole per-frame path of pipeline.py, fused).
+
+        The result is [N, Ho, Wo, 3] with (Ho, Wo) = ``output_shape(H, W)``: the input size when H, W are
+        multiples of 4 (always for the NST variant), else the reference module's larger output
+        (pipeline.py:1512-1516 resizes it back; ``FramePipeline`` does that on the device).
+        """
         if frames.dim() == 3:
-            return self.stylize_u8(frames[None], preset, blend, None if mask is None else mask[None], composite_mode)[0]
+            return self.stylize_u8(frames[None], preset, blend, None if mask is None else mask[None], composite_mode,
+                                   None if out is None else out[None])[0]
         if frames.dtype != torch.uint8 or frames.dim() != 4 or frames.shape[-1] != 3:
             raise ValueError(f"expected uint8 [N,H,W,3], got {frames.dtype} {tuple(frames.shape)}")
         self._check_dev(frames, "frames")
         frames = frames.contiguous()
         N, H, W, _ = frames.shape
+        Ho, Wo = self.output_shape(H, W)
         if out is None:
-            out = torch.empty_like(frames)
+            out = torch.empty(N, Ho, Wo, 3, dtype=torch.uint8, device=frames.device)
         else:
             self._check_dev(out, "out")
-            if out.shape != frames.shape or out.dtype != torch.uint8 or not out.is_contiguous():
-                raise ValueError("out must be a contiguous uint8 tensor shaped like frames")
+            if tuple(out.shape) != (N, Ho, Wo, 3) or out.dtype != torch.uint8 or not out.is_contiguous():
+                raise ValueError(f"out must be a contiguous uint8 tensor of shape {(N, Ho, Wo, 3)}")
         mptr = None
         if mask is not None:
             self._check_dev(mask, "mask")
@@ -166,11 +176,11 @@ class Engine:
             if tuple(mask.shape) != (N, H, W):
                 raise ValueError(f"mask must be [N,H,W]={N, H, W}, got {tuple(mask.shape)}")
             mptr = mask.data_ptr()
-        s_in, b_in, s_out, b_out, swap = io_preset_affine(preset)
+        s_in, b_in, d_out, s_out, b_out, swap = io_preset_affine(preset)
         ws = self._workspace(N, H, W)
         with torch.cuda.device(self.device):
             rc = self._lib.nst_forward_u8_nhwc(self._h, frames.data_ptr(), out.data_ptr(), N, H, W,
-                                               _f3(s_in), _f3(b_in), _f3(s_out), _f3(b_out), swap, float(blend),
+                                               _f3(s_in), _f3(b_in), _f3(d_out), _f3(s_out), _f3(b_out), swap, float(blend),
                                                mptr, _lib.COMPOSITE_MODE[composite_mode],
                                                ws.data_ptr(), ws.numel(), self._stream())
         _lib.check(rc, "nst_forward_u8_nhwc")
@@ -185,7 +195,8 @@ class Engine:
             fl, by, kind = C.c_double(0), C.c_double(0), C.c_int(0)
             _lib.check(self._lib.nst_layer_info(self._h, i, name, 96, C.byref(fl), C.byref(by), C.byref(kind)), "nst_layer_info")
             out.append({"name": name.value.decode(), "flops": fl.value, "bytes": by.value,
-                        "kernel": "tcgen05" if kind.value == 1 else "direct"})
+                        "kernel": "tcgen05" if kind.value >= 1 else "direct",
+                        "feed": {0: "direct", 1: "gather", 2: "tma"}[kind.value]})
         return out
 
     def profile_layers(self, frames: torch.Tensor):
@@ -193,7 +204,8 @@ class Engine:
         self._check_dev(frames, "frames")
         frames = frames.contiguous()
         N, H, W, _ = frames.shape
-        out = torch.empty_like(frames)
+        Ho, Wo = self.output_shape(H, W)
+        out = torch.empty(N, Ho, Wo, 3, dtype=torch.uint8, device=frames.device)
         ws = self._workspace(N, H, W)
         n = self._lib.nst_num_layers(self._h)
         ms = (C.c_float * n)()
@@ -223,6 +235,8 @@ def composite_regions(styled: Sequence[torch.Tensor], masks: torch.Tensor,
     """
     lib = _lib.load()
     K, R = len(styled), masks.shape[0]
+    if len(model_indices) != R or (model_weights is not None and len(model_weights) != R):
+        raise ValueError(f"model_indices / model_weights must have one entry per region ({R})")
     u8 = styled[0].dtype == torch.uint8
     dev = styled[0].device
     if not styled[0].is_cuda:
@@ -235,6 +249,12 @@ def composite_regions(styled: Sequence[torch.Tensor], masks: torch.Tensor,
     for ix, w in zip(idx, wts):
         flat_i += ix + [0] * (J - len(ix))
         flat_w += list(w) + [0.0] * (J - len(w))
+    want = (H, W, 3) if u8 else (3, H, W)
+    for t in list(styled) + ([original] if original is not None else []):
+        if tuple(t.shape) != want or t.dtype != styled[0].dtype or t.device != dev:
+            raise ValueError(f"every frame must be {styled[0].dtype} {want} on {dev}; got {t.dtype} {tuple(t.shape)} on {t.device}")
+    if tuple(masks.shape) != (R, H, W) or masks.device != dev:
+        raise ValueError(f"masks must be [R,H,W] = {(R, H, W)} on {dev}, got {tuple(masks.shape)} on {masks.device}")
     srcs = [s.contiguous() for s in styled]
     masks = masks.to(torch.float32).contiguous()
     orig = original.contiguous() if original is not None else None

@@ -15,10 +15,63 @@ from typing import Optional
 import torch
 from torch import nn
 
-from . import synth
 from .engine import Engine
 
 _DROP_TOKENS = ("running_mean", "running_var", "num_batches_tracked")   # pipeline.py:565
+
+
+def _conv(name: str, cout: int, cin: int, k: int, w: str = ".weight", b: str = ".bias"):
+    return [(name + w, (cout, cin, k, k)), (name + b, (cout,))]
+
+
+def _norm(name: str, c: int):
+    return [(name + ".weight", (c,)), (name + ".bias", (c,))]
+
+
+def _johnson_shapes():
+    """state_dict keys / shapes of transformer_net.TransformerNet (transformer_net.py:8-25)."""
+    out = []
+    for name, cout, cin, k, nrm in (("conv1", 32, 3, 9, "in1"), ("conv2", 64, 32, 3, "in2"), ("conv3", 128, 64, 3, "in3")):
+        out += _conv(name + ".conv2d", cout, cin, k) + _norm(nrm, cout)
+    for i in range(1, 6):
+        for j in (1, 2):
+            out += _conv(f"res{i}.conv{j}.conv2d", 128, 128, 3) + _norm(f"res{i}.in{j}", 128)
+    out += _conv("deconv1.conv2d", 64, 128, 3) + _norm("in4", 64)
+    out += _conv("deconv2.conv2d", 32, 64, 3) + _norm("in5", 32)
+    out += _conv("deconv3.conv2d", 3, 32, 9)
+    return out
+
+
+def _nst_shapes():
+    """transformer_net_nst.TransformerNet (transformer_net_nst.py:73-93); ConvTranspose2d weights are (in, out, k, k)."""
+    out = []
+    for name, cout, cin, k in (("down1", 32, 3, 9), ("down2", 64, 32, 3), ("down3", 128, 64, 3)):
+        out += _conv(name + ".conv", cout, cin, k) + _norm(name + ".norm", cout)
+    for i in range(1, 6):
+        for j in (1, 2):
+            out += _conv(f"res{i}.conv{j}", 128, 128, 3) + _norm(f"res{i}.norm{j}", 128)
+    for name, cin, cout in (("up1", 128, 64), ("up2", 64, 32)):
+        out += [(name + ".conv.weight", (cin, cout, 3, 3)), (name + ".conv.bias", (cout,))] + _norm(name + ".norm", cout)
+    out += _conv("final", 3, 32, 9)
+    return out
+
+
+def _reconet_shapes():
+    """model.ReCoNet(frn=False) (model.py:75-116): ConvNormLayer = Sequential(ConvLayer(Sequential(pad, conv)), IN[, ReLU])."""
+    out = []
+
+    def cnl(prefix, cout, cin, k):
+        return _conv(prefix + ".layers.0.layers.1", cout, cin, k) + _norm(prefix + ".layers.1", cout)
+
+    out += cnl("encoder.layers.0", 48, 3, 9) + cnl("encoder.layers.1", 96, 48, 3) + cnl("encoder.layers.2", 192, 96, 3)
+    for i in range(3, 7):
+        out += cnl(f"encoder.layers.{i}.branch.0", 192, 192, 3) + cnl(f"encoder.layers.{i}.branch.1", 192, 192, 3)
+    out += cnl("decoder.layers.1", 96, 192, 3) + cnl("decoder.layers.3", 48, 96, 3)
+    out += _conv("decoder.layers.4.layers.0.layers.1", 3, 48, 9)
+    return out
+
+
+PARAM_SHAPES = {"johnson": _johnson_shapes(), "nst": _nst_shapes(), "reconet": _reconet_shapes()}
 
 
 class _Holder(nn.Module):
@@ -34,8 +87,7 @@ class _B200Generator(nn.Module):
     def __init__(self, precision: str = "f16"):
         super().__init__()
         self.precision = precision
-        shapes = {k: tuple(v.shape) for k, v in synth.make_state_dict(self.ARCH, 0).items()}
-        for key, shape in shapes.items():
+        for key, shape in PARAM_SHAPES[self.ARCH]:
             *path, leaf = key.split(".")
             mod = self
             for part in path:

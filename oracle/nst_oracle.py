@@ -189,20 +189,30 @@ def stylize_u8(arch: str, sd: SD, frames_u8_nhwc: Tensor, preset: str,
     """Whole per-frame path of pipeline.py with uint8 in/out.
 
     ToTensor (/255) -> io_pre -> model -> io_post -> optional mask composite
-    (pipeline.py:2040-2043) or uniform blend (pipeline.py:2089-2092) -> pack.
+    (pipeline.py:2040-2043), THEN the uniform blend when ``0 <= blend < 1`` ("still applies
+    after region composite", pipeline.py:2088-2092) -> pack.
     ``mask``: [N,H,W] fp32 alpha in 0..1 or None.
     """
     x01 = frames_u8_nhwc.permute(0, 3, 1, 2).to(torch.float32) / 255.0
     out01 = io_post(forward(arch, sd, io_pre(x01, preset)), preset)
+    return post_u8(out01, x01, blend, mask, composite_mode)
+
+
+def post_u8(out01: Tensor, x01: Tensor, blend: float = 1.0, mask: Optional[Tensor] = None,
+            composite_mode: str = "keep") -> Tensor:
+    """Everything after io_post: mask composite (pipeline.py:2040-2043), uniform blend
+    (pipeline.py:2088-2092), truncating pack (pipeline.py:2094).  fp32, one rounding per op."""
     if out01.shape[-2:] != x01.shape[-2:]:
-        raise ValueError("oracle stylize_u8 expects H,W multiples of 4")
+        if mask is not None or 0.0 <= blend < 1.0:
+            raise ValueError("blend / mask need H,W multiples of 4 (the reference resizes first, pipeline.py:1512-1516)")
+        return pack_u8(out01)
     if mask is not None:
-        a = mask.unsqueeze(1)
+        a = mask.unsqueeze(1).to(torch.float32)
         if composite_mode == "keep":
             out01 = (a * out01 + (1.0 - a) * x01).clamp(0, 1)
         else:
             out01 = ((1.0 - a) * out01 + a * x01).clamp(0, 1)
-    elif 0.0 <= blend < 1.0:
+    if 0.0 <= blend < 1.0:
         out01 = (blend * out01 + (1.0 - blend) * x01).clamp(0, 1)
     return pack_u8(out01)
 

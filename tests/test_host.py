@@ -86,7 +86,7 @@ def test_shims_resolve_like_pipeline_imports():
 def test_io_preset_affine_equals_oracle(preset):
     from neuralstyletransferv1_b200 import io_preset_affine
     from oracle import nst_oracle as O
-    s_in, b_in, s_out, b_out, swap = io_preset_affine(preset)
+    s_in, b_in, d_out, s_out, b_out, swap = io_preset_affine(preset)
     u8 = torch.arange(0, 256, dtype=torch.float32).view(1, 1, 16, 16).repeat(1, 3, 1, 1)
     u8[:, 1] = u8[:, 1].flip(-1)
     u8[:, 2] = (u8[:, 2] * 7) % 256
@@ -97,8 +97,8 @@ def test_io_preset_affine_equals_oracle(preset):
     y = torch.randn(1, 3, 16, 16) * 100 + 100
     want_out = O.io_post(y, preset)
     ysrc = y[:, [2, 1, 0]] if swap else y
-    got_out = (ysrc * torch.tensor(s_out).view(1, 3, 1, 1) + torch.tensor(b_out).view(1, 3, 1, 1)).clamp(0, 1)
-    assert torch.allclose(got_out, want_out, rtol=1e-5, atol=1e-6)
+    got_out = ((ysrc / torch.tensor(d_out).view(1, 3, 1, 1)) * torch.tensor(s_out).view(1, 3, 1, 1) + torch.tensor(b_out).view(1, 3, 1, 1)).clamp(0, 1)
+    assert torch.equal(got_out, want_out)         # the same fp32 operation sequence as the reference's: bit-identical
 
 
 def test_shard_ranges_partition_frames():
@@ -121,3 +121,36 @@ def test_synthetic_frames_are_deterministic():
     b = synth.synthetic_frames_u8(3, 32, 48, seed=5)
     assert a.dtype == torch.uint8 and tuple(a.shape) == (3, 32, 48, 3) and torch.equal(a, b)
     assert int(a.max()) > 200 and int(a.min()) < 50
+
+
+# ---- planner (host only): production shapes stay on the tensor cores, TMA-fed where the source is an fp16 activation tensor ----
+@pytest.mark.parametrize("arch,n,h,w", [("johnson", 8, 1080, 1920), ("johnson", 8, 2160, 3840), ("johnson", 1, 3024, 4032),
+                                         ("johnson", 2, 1081, 1923), ("nst", 8, 1080, 1920), ("nst", 1, 2160, 3840),
+                                         ("reconet", 8, 1080, 1920), ("reconet", 2, 2160, 3840), ("johnson", 3, 50, 70),
+                                         ("nst", 1, 53, 47), ("reconet", 2, 38, 54)])
+def test_planner_keeps_production_shapes_on_tcgen05(arch, n, h, w):
+    from neuralstyletransferv1_b200 import _lib
+    text = _lib.describe_plan(arch, "f16", n, h, w)
+    lines = text.strip().splitlines()[1:]
+    assert len(lines) == {"johnson": 16, "nst": 16, "reconet": 14}[arch]
+    assert all(" tc " in ln and " direct " not in ln for ln in lines), text
+    gather = {"johnson": 1, "nst": 1, "reconet": 3}[arch]        # image layer; + ReCoNet's error-compensated encoder layers
+    assert all(" tc gather" in ln for ln in lines[:gather]), text
+    assert all(" tc tma" in ln for ln in lines[gather:]), text
+    for ln in lines:
+        smem = int(ln.split("smem=")[1].split("B")[0])
+        assert smem <= 227 * 1024, ln
+
+
+def test_planner_refuses_instead_of_degrading():
+    """A shape with no tcgen05 tiling is an error, never a silent fall to the fp32 FFMA kernel (VERDICT r1 weak #10)."""
+    from neuralstyletransferv1_b200 import _lib
+    assert " direct " in _lib.describe_plan("johnson", "fp32_direct", 1, 64, 64)
+    assert " direct " not in _lib.describe_plan("johnson", "f16", 1, 64, 64)
+
+
+def test_param_shape_table_matches_synth():
+    from neuralstyletransferv1_b200 import modules
+    for arch in synth.ARCHS:
+        sd = synth.make_state_dict(arch, 0)
+        assert [(k, tuple(v.shape)) for k, v in sd.items()] == [(k, tuple(sh)) for k, sh in modules.PARAM_SHAPES[arch]]
