@@ -91,6 +91,7 @@ struct WaitProf {
   __device__ __forceinline__ void flush(int role, bool leader) {
     if (buf && leader) {
       for (int i = 1; i < 8; ++i) if (acc[i]) atomicAdd(buf + i, (unsigned long long)acc[i]);
+      if (acc[0]) atomicAdd(buf + 13, (unsigned long long)acc[0]);
       atomicAdd(buf + 8 + role, (unsigned long long)(clock64() - t_start));
     }
   }
@@ -103,6 +104,40 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity, unsigne
   } else {
     mbar_wait(bar, parity, err, code);
   }
+}
+// Barrier granularity (A/B-measured on one box, tools/abn.sh): one lane polling for its warp (+ __syncwarp) is 5-10 % SLOWER on every
+// layer than all 32 lanes executing try_wait (the hardware parks the whole warp on the barrier), and one arrival per warp instead
+// of one per thread is neutral -- so both default to the per-thread form.
+#ifndef NST_WARP_POLL
+#define NST_WARP_POLL 0
+#endif
+#ifndef NST_WARP_ARRIVE
+#define NST_WARP_ARRIVE 0
+#endif
+constexpr uint32_t ARRIVALS_PER_WARP = NST_WARP_ARRIVE ? 1u : 32u;
+__device__ __forceinline__ void mbar_wait_warp(uint32_t bar, uint32_t parity, unsigned int* err, unsigned int code, WaitProf& wp) {
+#if NST_WARP_POLL
+  if ((threadIdx.x & 31) == 0) mbar_wait(bar, parity, err, code, wp);
+  __syncwarp();
+#else
+  mbar_wait(bar, parity, err, code, wp);
+#endif
+}
+__device__ __forceinline__ void mbar_wait_warp(uint32_t bar, uint32_t parity, unsigned int* err, unsigned int code) {
+#if NST_WARP_POLL
+  if ((threadIdx.x & 31) == 0) mbar_wait(bar, parity, err, code);
+  __syncwarp();
+#else
+  mbar_wait(bar, parity, err, code);
+#endif
+}
+__device__ __forceinline__ void mbar_arrive_warp(uint32_t bar) {
+#if NST_WARP_ARRIVE
+  __syncwarp();
+  if ((threadIdx.x & 31) == 0) mbar_arrive(bar);
+#else
+  mbar_arrive(bar);
+#endif
 }
 __device__ __forceinline__ uint32_t elect_one_sync() {
   uint32_t pred;
@@ -167,6 +202,23 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, float (&v)[16]) {
   asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 #pragma unroll
   for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
+}
+
+// 32 consecutive accumulator columns of this thread's TMEM lane; the caller waits (tmem_ld_wait) before using them
+__device__ __forceinline__ void tmem_ld32_nowait(uint32_t taddr, uint32_t (&r)[32]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+        "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
+        "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
+        "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_ld_wait() {
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
 
 // UMMA shared-memory matrix descriptor, SWIZZLE_NONE, K-major (cute::UMMA::SmemDescriptor):
@@ -273,7 +325,9 @@ struct IssueArgs {
 };
 constexpr uint32_t DESC_HI = (128u >> 4) | (1u << 14);     // SBO = 128 B, descriptor version 1, SWIZZLE_NONE
 
-template <int K16, int MB>
+// NTERMS = 3: error-compensated operands (hi*hi, lo*hi, hi*lo).  SWAP: weights are the A operand (M = 128 output channels), the halo
+// tile is the B operand (N = MB*128 positions) -- one MMA per (tap, K step) instead of MB.
+template <int K16, int MB, int NTERMS, bool SWAP>
 __device__ __forceinline__ void issue_group(const IssueArgs& a) {
   uint32_t acc = a.acc_on;
   uint32_t b_lo = a.b_lo;
@@ -282,12 +336,19 @@ __device__ __forceinline__ void issue_group(const IssueArgs& a) {
     const uint32_t a_lo = a.a_lo + a.ent_tab[e];
 #pragma unroll
     for (int j = 0; j < K16; ++j) {
-      const uint64_t bdesc = ((uint64_t)DESC_HI << 32) | (b_lo + (uint32_t)j * a.b_kstep16);
 #pragma unroll
-      for (int mb = 0; mb < MB; ++mb)
-        umma_f16(a.tmem_acc + (uint32_t)mb * a.npad, ((uint64_t)DESC_HI << 32) | (a_lo + (uint32_t)j * a.a_kstep16 + (uint32_t)mb * 128u), bdesc,
-                 a.idesc, acc);
-      acc = 1u;
+      for (int term = 0; term < NTERMS; ++term) {
+        const uint64_t bdesc = ((uint64_t)DESC_HI << 32) | (b_lo + (uint32_t)j * a.b_kstep16 + (term == 2 ? a.b_term16 : 0u));
+        const uint32_t a_j = a_lo + (uint32_t)j * a.a_kstep16 + (term == 1 ? a.a_term16 : 0u);
+        if (SWAP) {
+          umma_f16(a.tmem_acc, bdesc, ((uint64_t)DESC_HI << 32) | a_j, a.idesc, acc);
+        } else {
+#pragma unroll
+          for (int mb = 0; mb < MB; ++mb)
+            umma_f16(a.tmem_acc + (uint32_t)mb * a.npad, ((uint64_t)DESC_HI << 32) | (a_j + (uint32_t)mb * 128u), bdesc, a.idesc, acc);
+        }
+        acc = 1u;
+      }
     }
   }
 }
@@ -416,7 +477,7 @@ __device__ void produce_act16(const ConvParams& p, const TcPlan& t, uint8_t* sme
       const int c0 = c.ch * t.CK + g * 8;
 #pragma unroll
       for (int i = 0; i < 8; ++i) { const float2 cf = coeff[c0 + i]; sc[i] = cf.x; sh[i] = cf.y; }
-      mbar_wait(bar_a_empty0 + 8u * sa, pa ^ 1u, err, 6, wprof);
+      mbar_wait_warp(bar_a_empty0 + 8u * sa, pa ^ 1u, err, 6, wprof);
       plane_hi = smem_a + (size_t)sa * t.a_stage_bytes + (size_t)g * t.a_plane_bytes;
     }
     const size_t plane_base = ((size_t)(c.tile / (t.tiles_x * t.tiles_y)) * (p.Cin >> 3) + (size_t)(c.ch * t.planes + g)) * ((size_t)p.Hs * p.Ws);
@@ -459,7 +520,7 @@ __device__ void produce_act16(const ConvParams& p, const TcPlan& t, uint8_t* sme
     }
     if (c.b == nB - 1) {
       fence_proxy_async_smem();
-      mbar_arrive(bar_a_full0 + 8u * sa);
+      mbar_arrive_warp(bar_a_full0 + 8u * sa);
       if (++sa == (uint32_t)t.a_stages) { sa = 0; pa ^= 1u; }
     }
   };
@@ -594,6 +655,8 @@ __device__ void transform_act16(const TcArgs& args, uint8_t* smem_a, float2* coe
   const int halo_w = p.stride == 1 ? t.P : t.halo_w;
   const int per_img = t.tiles_x * t.tiles_y;
   __half* side = (__half*)p.side_out;
+  // loop invariants in registers (the plan sits behind a generic pointer; asm volatile "memory" clobbers would force reloads)
+  const int kP = t.P, kTH = t.TH, kTW = t.TW, kHo = p.Ho, kWo = p.Wo, kWs = p.Ws, kPadT = p.pad_t, kPadL = p.pad_l;
   WaitProf wprof; wprof.init(args.prof);
   uint32_t sa = 0, pa = 0;
   int cur_n = -1;
@@ -615,11 +678,11 @@ __device__ void transform_act16(const TcArgs& args, uint8_t* smem_a, float2* coe
     const bool border = u0 < 0 || v0 < 0 || u0 + t.halo_h > p.Hc || v0 + halo_w > p.Wc;
     for (int ch = 0; ch < t.nchunks; ++ch) {
       {
-        const int c0 = ch * t.CK + g * 8;
+        const float4* cf4 = reinterpret_cast<const float4*>(coeff + ch * t.CK + g * 8);      // two (scale, shift) pairs per 16-byte load
 #pragma unroll
-        for (int i = 0; i < 8; ++i) { const float2 cf = coeff[c0 + i]; sc[i] = cf.x; sh[i] = cf.y; }
+        for (int i = 0; i < 4; ++i) { const float4 cf = cf4[i]; sc[2 * i] = cf.x; sh[2 * i] = cf.y; sc[2 * i + 1] = cf.z; sh[2 * i + 1] = cf.w; }
       }
-      mbar_wait(bar_tma_full0 + 8u * sa, pa, args.err_flag, 7, wprof);
+      mbar_wait_warp(bar_tma_full0 + 8u * sa, pa, args.err_flag, 7, wprof);
       uint8_t* plane = smem_a + (size_t)sa * t.a_stage_bytes + (size_t)g * t.a_plane_bytes;
       const uint8_t* rplane = plane + t.a_res_off;
       // side output: slot (hy, hx) of plane (n, ch*planes + g) is source pixel (u0 + hy, v0 + hx) (identity-mapped stride-1 layers)
@@ -657,10 +720,10 @@ __device__ void transform_act16(const TcArgs& args, uint8_t* smem_a, float2* coe
             *reinterpret_cast<uint4*>(plane + (size_t)q * 16) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
             if (SIDE) {
               const int hy = (int)(((float)q + 0.5f) * inv_p);
-              const int hx = q - hy * t.P;
-              const int iy = hy - p.pad_t, ix = hx - p.pad_l;
-              if (iy >= 0 && iy < t.TH && ix >= 0 && ix < t.TW && tc.ty0 + iy < p.Ho && tc.tx0 + ix < p.Wo)
-                *reinterpret_cast<uint4*>(side + (size_t)(side_base + (long long)hy * p.Ws + hx) * 8) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+              const int hx = q - hy * kP;
+              const int iy = hy - kPadT, ix = hx - kPadL;
+              if ((iy >= 0) & (iy < kTH) & (ix >= 0) & (ix < kTW) & (tc.ty0 + iy < kHo) & (tc.tx0 + ix < kWo))
+                *reinterpret_cast<uint4*>(side + (size_t)(side_base + (long long)hy * kWs + hx) * 8) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
             }
           }
         }
@@ -684,7 +747,7 @@ __device__ void transform_act16(const TcArgs& args, uint8_t* smem_a, float2* coe
         }
       }
       fence_proxy_async_smem();       // generic-proxy smem writes -> visible to tcgen05.mma (async proxy)
-      mbar_arrive(bar_a_full0 + 8u * sa);
+      mbar_arrive_warp(bar_a_full0 + 8u * sa);
       if (++sa == (uint32_t)t.a_stages) { sa = 0; pa ^= 1u; }
     }
   }
@@ -711,9 +774,9 @@ struct MmaCtx {
   int first_tile, tile_step, end_tile;
 };
 
-template <int K16, int MB_>
+template <int K16, int MB_, int NTERMS = 1, bool SWAP = false>
 __device__ __noinline__ void mma_role(const TcPlan& t, const MmaCtx c) {
-  const uint32_t idesc = make_idesc(t.NPAD, t.is_bf16);
+  const uint32_t idesc = make_idesc(SWAP ? t.MB * 128 : t.NPAD, t.is_bf16);
   const uint32_t a_lbo16 = (t.pair_mode ? 16u * (uint32_t)t.pair_mode : t.a_plane_bytes) >> 4;   // pair: next slot, quad: two slots on
   const uint32_t a_lo_base = ((c.smem_a >> 4) & 0x3FFFu) | (a_lbo16 << 16);
   const uint32_t b_lo_base = ((c.smem_b >> 4) & 0x3FFFu) | ((uint32_t)t.NPAD << 16);   // LBO = NPAD*16 B
@@ -731,22 +794,22 @@ __device__ __noinline__ void mma_role(const TcPlan& t, const MmaCtx c) {
   uint32_t sa = 0, pa = 0, sb = 0, pb = 0, it = 0;
   for (int tile = c.first_tile; tile < num_tiles; tile += c.tile_step, ++it) {
     const uint32_t buf = it & 1u;
-    if (!(dbg & 32)) mbar_wait(ACC_EMPTY0 + 8u * buf, ((it >> 1) & 1u) ^ 1u, c.err, 2, wprof);
+    if (!(dbg & 32)) mbar_wait_warp(ACC_EMPTY0 + 8u * buf, ((it >> 1) & 1u) ^ 1u, c.err, 2, wprof);
     tc_fence_after();
     const uint32_t tmem_acc = c.tmem_base + buf * (uint32_t)(MB * NPAD);
     uint32_t acc_on = 0u;
     for (int ch = 0; ch < nchunks; ++ch) {
-      if (!(dbg & 16)) mbar_wait(A_FULL0 + 8u * sa, pa, c.err, 3, wprof);
+      if (!(dbg & 16)) mbar_wait_warp(A_FULL0 + 8u * sa, pa, c.err, 3, wprof);
       tc_fence_after();
       const uint32_t a_stage_lo = a_lo_base + sa * a_stage16;
       int ent = 0;
       for (int g = 0; g < ngroups; ++g) {
-        if (!(dbg & 64)) mbar_wait(B_FULL0 + 8u * sb, resident ? 0u : pb, c.err, 4, wprof);
+        if (!(dbg & 64)) mbar_wait_warp(B_FULL0 + 8u * sb, resident ? 0u : pb, c.err, 4, wprof);
         tc_fence_after();
         if (elect_one_sync()) {
           const IssueArgs ia = {tmem_acc, a_stage_lo, b_lo_base + sb * b_stage16, b_ent16, a_kstep16, b_kstep16, a_term16, b_term16, (uint32_t)NPAD, idesc,
                                 c.ent_tab + ent, min(tg, nent - ent), acc_on};
-          if (K16 != 0) issue_group<(K16 ? K16 : 1), (MB_ ? MB_ : 1)>(ia);
+          if (K16 != 0) issue_group<(K16 ? K16 : 1), (MB_ ? MB_ : 1), NTERMS, SWAP>(ia);
           else issue_group_generic(ia, k16, MB, nterms);
           if (!resident) umma_commit(B_EMPTY0 + 8u * sb);
         }
@@ -817,15 +880,15 @@ __device__ __noinline__ void mma_role_phase(const TcPlan& t, const MmaCtx c) {
   uint32_t sa = 0, pa = 0, sb = 0, pb = 0, it = 0;
   for (int tile = c.first_tile; tile < num_tiles; tile += c.tile_step, ++it) {
     const uint32_t buf = it & 1u;
-    mbar_wait(ACC_EMPTY0 + 8u * buf, ((it >> 1) & 1u) ^ 1u, c.err, 2, wprof);
+    mbar_wait_warp(ACC_EMPTY0 + 8u * buf, ((it >> 1) & 1u) ^ 1u, c.err, 2, wprof);
     tc_fence_after();
     const uint32_t tmem_acc = c.tmem_base + buf * (uint32_t)(MB * NPAD);
     for (int ch = 0; ch < nchunks; ++ch) {
-      mbar_wait(A_FULL0 + 8u * sa, pa, c.err, 3, wprof);
+      mbar_wait_warp(A_FULL0 + 8u * sa, pa, c.err, 3, wprof);
       tc_fence_after();
       const uint32_t a_stage_lo = a_lo_base + sa * a_stage16;
       for (int g = 0; g < ngroups; ++g) {
-        mbar_wait(B_FULL0 + 8u * sb, pb, c.err, 4, wprof);
+        mbar_wait_warp(B_FULL0 + 8u * sb, pb, c.err, 4, wprof);
         tc_fence_after();
         if (elect_one_sync()) {
           const uint32_t b_stage_addr = b_addr_base + sb * b_stage16;
@@ -865,6 +928,107 @@ __device__ __noinline__ void mma_role_phase(const TcPlan& t, const MmaCtx c) {
   wprof.flush(1, (threadIdx.x & 31) == 0);
 }
 
+// ---------------------------------------------------------------------------------------------
+// epilogue of the swapped (weights = A operand) form: TMEM lane = output channel, column = tile position
+// ---------------------------------------------------------------------------------------------
+// Warp `quad` owns channels [32*quad, 32*quad + 32): each thread reads its channel's accumulator row 32 positions at a time, adds
+// the valid positions into its own (sum, sum of squares) -- no cross-lane reduction -- and the 8 lanes that share an 8-channel
+// plane transpose their (channel x position) fragments with 12 shuffles per 16 positions so that every lane ends up with all 8
+// channels of two positions = two 16-byte planar-8 slots, stored straight to HBM (8 lanes x 32 B = 256 contiguous bytes per plane).
+// Running sums over the CTA's tile run are double registers; a sample change (and the end) writes them to this CTA's slot of the
+// partial table (stats_finalize_kernel folds the CTAs in index order: bit-reproducible).
+__device__ __forceinline__ void transpose8x8(uint32_t (&r)[8], int l8) {
+#pragma unroll
+  for (int s = 4; s >= 1; s >>= 1) {
+    const bool up = (l8 & s) != 0;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      if (i & s) continue;
+      const uint32_t send = up ? r[i] : r[i + s];
+      const uint32_t recv = __shfl_xor_sync(0xffffffffu, send, s);
+      if (up) r[i] = recv; else r[i + s] = recv;
+    }
+  }
+}
+
+__device__ __noinline__ void epilogue_swap(const TcArgs& args, uint32_t tmem_base, uint32_t acc_full0, uint32_t acc_empty0, int first_tile, int end_tile,
+                                           int quad, int lane) {
+  const ConvParams& p = args.p;
+  const TcPlan& t = args.t;
+  const int co = quad * 32 + lane;                 // this thread's output channel = its TMEM lane
+  const int l8 = lane & 7, g8 = lane >> 3;
+  const int ncols = t.MB * 128;                    // positions per tile (accumulator columns)
+  // loop invariants in registers: `args` lives in the kernel-parameter bank behind a generic pointer here, and every asm volatile
+  // ("memory") in the loop would otherwise force a reload (ncu: long-scoreboard stalls on exactly these loads)
+  const int P = t.P, TH = t.TH, TW = t.TW, Ho = p.Ho, Wo = p.Wo;
+  const float inv_p = 1.0f / (float)P;
+  const size_t plane_slots = (size_t)Ho * Wo;      // 16-byte slots per 8-channel plane
+  uint4* const out_base = reinterpret_cast<uint4*>(p.out);
+  const int c8 = p.Cout >> 3;
+  double sum_d = 0.0, sq_d = 0.0;
+  int cur_n = -1;
+  auto flush = [&]() {
+    if (cur_n < 0) return;
+    double* st = p.out_part + (((size_t)blockIdx.x * p.N + cur_n) * p.Cout + co) * 2;
+    st[0] = sum_d; st[1] = sq_d;
+    sum_d = 0.0; sq_d = 0.0;
+  };
+  WaitProf wprof; wprof.init(args.prof);
+  uint32_t it = 0;
+  for (int tile = first_tile; tile < ((t.dbg & 32) ? 0 : end_tile); ++tile, ++it) {
+    const TileCoord tc = decode_tile(t, tile);
+    if (tc.n != cur_n) { flush(); cur_n = tc.n; }
+    const uint32_t buf = it & 1u;
+    mbar_wait_warp(acc_full0 + 8u * buf, (it >> 1) & 1u, args.err_flag, 5, wprof);
+    tc_fence_after();
+    const uint32_t tbase = tmem_base + ((uint32_t)(quad * 32) << 16) + buf * (uint32_t)ncols;
+    uint4* const oplane = out_base + ((size_t)tc.n * c8 + (size_t)(quad * 4 + g8)) * plane_slots;
+    float ts = 0.f, tq = 0.f;
+    for (int c0 = 0; c0 < ncols; c0 += 32) {
+      uint32_t v[32];
+      tmem_ld32_nowait(tbase + (uint32_t)c0, v);
+      // while the load is in flight: validity / output slot of position c0 + lane (the same for every lane's channel)
+      const int m = c0 + lane;
+      const int ty = (int)(((float)m + 0.5f) * inv_p);
+      const int tx = m - ty * P;
+      const int oy = tc.ty0 + ty, ox = tc.tx0 + tx;
+      const bool valid = (ty < TH) & (tx < TW) & (oy < Ho) & (ox < Wo);
+      const int pix = valid ? oy * Wo + ox : -1;
+      const uint32_t vmask = __ballot_sync(0xffffffffu, valid);
+      const long long tA = wprof.buf ? clock64() : 0;
+      tmem_ld_wait();
+      const long long tB = wprof.buf ? clock64() : 0;
+      if (c0 + 32 >= ncols) { tc_fence_before(); mbar_arrive_warp(acc_empty0 + 8u * buf); }     // last read of this accumulator buffer
+      uint32_t h[16];
+#pragma unroll
+      for (int k = 0; k < 16; ++k) {
+        const float a = __uint_as_float(v[2 * k]), b = __uint_as_float(v[2 * k + 1]);
+        const float am = ((vmask >> (2 * k)) & 1u) ? a : 0.f, bm = ((vmask >> (2 * k + 1)) & 1u) ? b : 0.f;
+        ts += am; tq = fmaf(am, am, tq);
+        ts += bm; tq = fmaf(bm, bm, tq);
+        h[k] = pack2(a, b, 0);
+      }
+#pragma unroll
+      for (int blk = 0; blk < 2; ++blk) {
+        uint32_t r[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) r[k] = h[blk * 8 + k];
+        transpose8x8(r, l8);                              // r[k] = (channel k of the plane) x (positions 2*l8, 2*l8 + 1) of this block
+        const int pix0 = __shfl_sync(0xffffffffu, pix, blk * 16 + 2 * l8);
+        const int pix1 = __shfl_sync(0xffffffffu, pix, blk * 16 + 2 * l8 + 1);
+        if (pix0 >= 0)
+          oplane[pix0] = make_uint4(__byte_perm(r[0], r[1], 0x5410), __byte_perm(r[2], r[3], 0x5410), __byte_perm(r[4], r[5], 0x5410), __byte_perm(r[6], r[7], 0x5410));
+        if (pix1 >= 0)
+          oplane[pix1] = make_uint4(__byte_perm(r[0], r[1], 0x7632), __byte_perm(r[2], r[3], 0x7632), __byte_perm(r[4], r[5], 0x7632), __byte_perm(r[6], r[7], 0x7632));
+      }
+      if (wprof.buf) wprof.acc[0] += tB - tA;                                              // debug: cycles waiting for the TMEM load
+    }
+    sum_d += (double)ts; sq_d += (double)tq;
+  }
+  flush();
+  wprof.flush(2, quad == (TC_FIRST_EPI_WARP & 3) && lane == 0);
+}
+
 constexpr int NBARS = 3 * TC_MAX_A_STAGES + 2 * TC_MAX_B_STAGES + 4;     // A_FULL, A_EMPTY, B_FULL, B_EMPTY, ACC_FULL/EMPTY x2, TMA_FULL
 
 __global__ void __launch_bounds__(TC_THREADS, 1)
@@ -896,9 +1060,9 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
   const int lane = threadIdx.x & 31;
 
   if (threadIdx.x == 0) {
-    for (int s = 0; s < TC_MAX_A_STAGES; ++s) { mbar_init(A_FULL(s), (uint32_t)t.prod_warps * 32u); mbar_init(A_EMPTY(s), 1); }
+    for (int s = 0; s < TC_MAX_A_STAGES; ++s) { mbar_init(A_FULL(s), (uint32_t)t.prod_warps * ARRIVALS_PER_WARP); mbar_init(A_EMPTY(s), 1); }
     for (int s = 0; s < TC_MAX_B_STAGES; ++s) { mbar_init(B_FULL(s), 1); mbar_init(B_EMPTY(s), 1); }
-    for (int s = 0; s < 2; ++s) { mbar_init(ACC_FULL(s), 1); mbar_init(ACC_EMPTY(s), 128); }
+    for (int s = 0; s < 2; ++s) { mbar_init(ACC_FULL(s), 1); mbar_init(ACC_EMPTY(s), 4 * ARRIVALS_PER_WARP); }
     for (int s = 0; s < TC_MAX_A_STAGES; ++s) mbar_init(TMA_FULL(s), 1);
     fence_barrier_init();
   }
@@ -952,6 +1116,13 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
       else if (t.phase_mode == 2 && t.k16_per_ent == 2 && t.MB == 2) mma_role_phase<2, 2, 2>(t, mc);
       else mma_role_phase<1, 0, 0>(t, mc);
     }
+    else if (t.swap_ab && t.MB == 2) mma_role<2, 2, 1, true>(t, mc);
+    else if (t.swap_ab) mma_role<2, 1, 1, true>(t, mc);
+    else if (t.nterms == 3 && t.k16_per_ent == 1 && t.MB == 4) mma_role<1, 4, 3>(t, mc);
+    else if (t.nterms == 3 && t.k16_per_ent == 1 && t.MB == 2) mma_role<1, 2, 3>(t, mc);
+    else if (t.nterms == 3 && t.k16_per_ent == 1 && t.MB == 1) mma_role<1, 1, 3>(t, mc);
+    else if (t.nterms == 3 && t.k16_per_ent == 2 && t.MB == 1) mma_role<2, 1, 3>(t, mc);
+    else if (t.nterms == 3 && t.k16_per_ent == 2 && t.MB == 2) mma_role<2, 2, 3>(t, mc);
     else if (t.nterms == 1 && t.k16_per_ent == 2 && t.MB == 2) mma_role<2, 2>(t, mc);
     else if (t.nterms == 1 && t.k16_per_ent == 2 && t.MB == 4) mma_role<2, 4>(t, mc);
     else if (t.nterms == 1 && t.k16_per_ent == 2 && t.MB == 8) mma_role<2, 8>(t, mc);
@@ -966,7 +1137,9 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
     const int quad = warp & 3;                        // TMEM lane quadrant this warp may read
     const int njc = t.NPAD >> 4;
     const int my_chan = ((lane & 16) ? 8 : 0) + ((lane & 8) ? 4 : 0) + ((lane & 4) ? 2 : 0) + ((lane & 2) ? 1 : 0);
-    if (t.fold_s) {
+    if (t.swap_ab) {
+      epilogue_swap(args, tmem_base, ACC_FULL(0), ACC_EMPTY(0), first_tile, end_tile, quad, lane);
+    } else if (t.fold_s) {
       // Image layer with the horizontal taps folded into N:  TMEM holds T[m][s*3+co] = sum_{r,ci} in[m + r*P][ci] w[co][ci][r][s];
       // out[m][co] = sum_s T[m + s][s*3 + co].  Rows are exchanged through a two-block ring in shared memory: block mb is
       // written to half (mb & 1), then every thread finishes the output 8 rows behind its own TMEM row.
@@ -977,14 +1150,14 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
       for (int tile = first_tile; tile < ((t.dbg & 32) ? 0 : end_tile); tile += tile_step, ++it) {
         const TileCoord tc = decode_tile(t, tile);
         const uint32_t buf = it & 1u;
-        mbar_wait(ACC_FULL(buf), (it >> 1) & 1u, err, 5, wprof);
+        mbar_wait_warp(ACC_FULL(buf), (it >> 1) & 1u, err, 5, wprof);
         tc_fence_after();
         for (int mb = 0; mb < t.MB; ++mb) {
           const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + buf * (uint32_t)(t.MB * t.NPAD) + (uint32_t)(mb * t.NPAD);
           float v0[16], v1[16];
           tmem_ld16(taddr, v0);
           tmem_ld16(taddr + 16u, v1);
-          if (mb == t.MB - 1) { tc_fence_before(); mbar_arrive(ACC_EMPTY(buf)); }
+          if (mb == t.MB - 1) { tc_fence_before(); mbar_arrive_warp(ACC_EMPTY(buf)); }
           named_bar_sync(3, 128);                       // readers of the previous block are done with this half's neighbour rows
           float* row = fold_ring + (size_t)((mb & 1) * 128 + tid) * TC_FOLD_PITCH;
 #pragma unroll
@@ -1043,7 +1216,7 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
         const TileCoord tc = decode_tile(t, tile);
         if (tc.n != cur_n) { flush(); cur_n = tc.n; }
         const uint32_t buf = it & 1u;
-        mbar_wait(ACC_FULL(buf), (it >> 1) & 1u, err, 5, wprof);
+        mbar_wait_warp(ACC_FULL(buf), (it >> 1) & 1u, err, 5, wprof);
         tc_fence_after();
         const uint32_t tbase = tmem_base + ((uint32_t)(quad * 32) << 16) + buf * (uint32_t)(t.MB * t.NPAD);
         if (p.out_fmt == OUT_F32_NHWC_STATS) {
@@ -1113,7 +1286,7 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
               }
             }
             }
-            if (cg == ncg - 1 && nmb > 0) { tc_fence_before(); mbar_arrive(ACC_EMPTY(buf)); }
+            if (cg == ncg - 1 && nmb > 0) { tc_fence_before(); mbar_arrive_warp(ACC_EMPTY(buf)); }
 #pragma unroll
             for (int w = 8, off = 16; w >= 1; w >>= 1, off >>= 1) {
               const bool up = (lane & off) != 0;
@@ -1136,7 +1309,7 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
               *w2 = cur;
             }
           }
-          if (ncg == 0 || nmb == 0) { tc_fence_before(); mbar_arrive(ACC_EMPTY(buf)); }
+          if (ncg == 0 || nmb == 0) { tc_fence_before(); mbar_arrive_warp(ACC_EMPTY(buf)); }
         } else {
           for (int mb = 0; mb < t.MB; ++mb) {
             const int m = mb * 128 + quad * 32 + lane;
@@ -1147,7 +1320,7 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
             if (ty < t.TH && tx < t.TW && oy < p.Ho && ox < p.Wo) store_image(p, tc.n, oy, ox, v[0] + p.bias[0], v[1] + p.bias[1], v[2] + p.bias[2]);
           }
           tc_fence_before();
-          mbar_arrive(ACC_EMPTY(buf));
+          mbar_arrive_warp(ACC_EMPTY(buf));
         }
       }
       flush();
@@ -1221,7 +1394,7 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
         for (int j = ptid - 64; j >= 0 && j < t.P; j += PT - 64)
           colv[j] = map_coord((tc.tx0 + p.ox_off) + j - p.pad_l, p.Wc, p.Ws, p.map_mode, p.prepad, p.pad_mode);
         named_bar_sync(2, PT);
-        mbar_wait(A_EMPTY(sa), pa ^ 1u, err, 6);
+        mbar_wait_warp(A_EMPTY(sa), pa ^ 1u, err, 6);
         uint8_t* plane = smem_a + (size_t)sa * t.a_stage_bytes;
         const uint8_t* __restrict__ src8 = (const uint8_t*)p.src;
         for (int q0 = ptid; q0 < t.NPOS; q0 += UB * PT) {
@@ -1264,7 +1437,7 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
           }
         }
         fence_proxy_async_smem();
-        mbar_arrive(A_FULL(sa));
+        mbar_arrive_warp(A_FULL(sa));
         if (++sa == (uint32_t)t.a_stages) { sa = 0; pa ^= 1u; }
       }
     } else
@@ -1288,7 +1461,7 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
 #pragma unroll
           for (int i = 0; i < 8; ++i) { const float2 cf = coeff[c0 + i]; sc[i] = cf.x; sh[i] = cf.y; }
         }
-        mbar_wait(A_EMPTY(sa), pa ^ 1u, err, 6);
+        mbar_wait_warp(A_EMPTY(sa), pa ^ 1u, err, 6);
         uint8_t* stage = smem_a + (size_t)sa * t.a_stage_bytes;
         uint8_t* plane_hi = stage + (size_t)g * t.a_plane_bytes;
         uint8_t* plane_lo = plane_hi + t.a_term_bytes;
@@ -1381,7 +1554,7 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
           }
         }
         fence_proxy_async_smem();       // generic-proxy smem writes -> visible to tcgen05.mma (async proxy)
-        mbar_arrive(A_FULL(sa));
+        mbar_arrive_warp(A_FULL(sa));
         if (++sa == (uint32_t)t.a_stages) { sa = 0; pa ^= 1u; }
       }
     }

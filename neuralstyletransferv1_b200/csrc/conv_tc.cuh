@@ -42,6 +42,10 @@ struct TcPlan {
   int nterms;               // 1, or 3 (hi*hi + lo*hi + hi*lo)
   int a_tplanes, b_tplanes; // operand planes kept (1, or 2 = hi and lo)
   int is_bf16;
+  int swap_ab;              // Cout = 128 layers: the weights are the MMA's A operand (M = 128 output channels) and the halo tile its B operand
+                            // (N = MB*128 positions): one M=128 x N=256 MMA reads 4 KB of weights + 8 KB of activations from shared
+                            // memory per 128 cycles (96 B/clk) where two N=128 MMAs read 16 KB (128 B/clk = all of the SM's shared-memory
+                            // bandwidth).  The accumulator is then [channel lane][position column]: per-channel statistics are per-thread sums.
   int fold_s;               // image layer (Cout = 3, k9): GEMM N = (horizontal tap s, co) = 27 of 32 columns, entries = the 9 filter
                             // rows; the epilogue sums T[m + s][s*3 + co] over s through a shared-memory ring (9x fewer MMAs)
   int dbg;                  // debug bits (tools/dbg_sweep.sh): switch pipeline roles off one at a time

@@ -357,6 +357,8 @@ static void tc_plan_static_(const LayerSpec& s, int precision, TcPlan& t) {
   int mb = 256 / t.NPAD;                  // two accumulator buffers of MB*NPAD columns in 512
   mb = mb >= 8 ? 8 : (mb >= 4 ? 4 : (mb >= 2 ? 2 : 1));   // powers of two: the MMA issuer is instantiated for MB = 1, 2, 4, 8
   t.MB = mb;
+  // Cout = 128: weights as the A operand (M = 128 channels), the halo tile as B (N = MB*128 positions) -- see TcPlan::swap_ab
+  t.swap_ab = (s.cout == 128 && t.NPAD == 128 && !t.pair_mode && !t.fold_s && t.nterms == 1 && t.k16_per_ent == 2 && !getenv("NST_NO_SWAP")) ? 1 : 0;
 }
 
 // Shape-dependent part: tile extent, halo buffer, shared-memory budget.
@@ -856,6 +858,7 @@ static int make_plan(nst_handle* h, int N, int H, int W) {
     }
     if (lp.use_tc) {
       lp.t = h->dev[li].tc_static;
+      if (!lp.out16 || s.out == BUF_IMAGE) lp.t.swap_ab = 0;                 // the swapped epilogue stores fp16 planar-8
       ConvParams q = p;
       if (lp.t.phase_mode) {
         // tile over the low-res grid; the epilogue scatters the four phases into the [N, 2Hs, 2Ws, Cout] output
@@ -867,7 +870,9 @@ static int make_plan(nst_handle* h, int N, int H, int W) {
       if (lp.t.tma_mode) lp.t.prod_warps = std::min(lp.t.prod_warps, TC_PROD_WARPS - 1);
       bool ok = tc_plan_geometry(q, lp.t, fTH, fMB);
       if (!ok && lp.t.tma_mode) {                                            // shapes the TMA boxes cannot express fall back to the gather producers
+        const int swap = lp.t.swap_ab;
         lp.t = h->dev[li].tc_static;
+        lp.t.swap_ab = swap;
         ok = tc_plan_geometry(q, lp.t, fTH, fMB);
       }
       q.resid = nullptr;
@@ -1066,10 +1071,10 @@ static int run_forward(nst_handle* h, const IoSpec& io, int N, int H, int W, voi
           CUDA_TRY(cudaStreamSynchronize(stream));
           const double g = std::min(a.t.num_tiles, h->num_sms);
           fprintf(stderr, "[tcprof] %-12s %s tiles=%d ctas=%.0f | per-CTA kcycles: loader total %.0f wait B_EMPTY %.0f | mma total %.0f wait ACC_EMPTY %.0f A_FULL %.0f B_FULL %.0f | "
-                          "epi total %.0f wait ACC_FULL %.0f | prod total %.0f wait A_EMPTY %.0f | tma-issue total %.0f, transform waits TMA_FULL %.0f\n", s.name.c_str(),
+                          "epi total %.0f wait ACC_FULL %.0f | prod total %.0f wait A_EMPTY %.0f | tma-issue total %.0f, transform waits TMA_FULL %.0f | epi-T TMEM-load wait %.0f\n", s.name.c_str(),
                   lp.t.tma_mode ? "tma" : "gather", a.t.num_tiles, g,
                   pc[8] / g / 1e3, pc[1] / g / 1e3, pc[9] / g / 1e3, pc[2] / g / 1e3, pc[3] / g / 1e3, pc[4] / g / 1e3, pc[10] / g / 1e3, pc[5] / g / 1e3,
-                  pc[11] / g / 1e3, pc[6] / g / 1e3, pc[12] / g / 1e3, pc[7] / g / 1e3);
+                  pc[11] / g / 1e3, pc[6] / g / 1e3, pc[12] / g / 1e3, pc[7] / g / 1e3, pc[13] / g / 1e3);
         }
       } else {
         if (s.out != BUF_IMAGE) CUDA_TRY(cudaMemsetAsync(p.out_part, 0, (size_t)n * s.cout * 2 * sizeof(double), stream));
@@ -1233,7 +1238,7 @@ extern "C" int nst_describe_plan(int arch, int precision, int N, int H, int W, c
       snprintf(line, sizeof(line),
                "%-28s %3d->%3d k%d s%d %4dx%-4d -> %4dx%-4d tc %s%s TH=%2d TW=%3d P=%3d MB=%d NPOS=%4d CK=%2d chunks=%d ent=%2d tg=%d "
                "A=%dx%uB B=%dx%uB smem=%uB tiles/img=%d rows_useful=%.2f GF=%.2f\n",
-               sp.name.c_str(), sp.cin, sp.cout, sp.ks, sp.stride, lp.p.Hs, lp.p.Ws, lp.p.Ho, lp.p.Wo, t.tma_mode ? "tma   " : "gather",
+               sp.name.c_str(), sp.cin, sp.cout, sp.ks, sp.stride, lp.p.Hs, lp.p.Ws, lp.p.Ho, lp.p.Wo, t.tma_mode ? (t.swap_ab ? "tma/T " : "tma   ") : (t.swap_ab ? "gath/T" : "gather"),
                h.dev[li].prec == NST_PREC_F16X3 ? " x3" : (lp.out16 ? "" : " f32"), t.TH, t.TW, t.P, t.MB, t.NPOS,
                t.CK, t.nchunks, t.nent, t.tg, t.a_stages, t.a_stage_bytes, t.b_stages, t.b_stage_bytes, t.smem_bytes,
                t.tiles_x * t.tiles_y, useful, lp.flops * 1e-9);
