@@ -567,7 +567,7 @@ __device__ __forceinline__ void tile_origin(const ConvParams& p, const TileCoord
 }
 
 // Loader: one thread walks (tile, channel chunk) in MMA order and keeps the operand ring full.
-__device__ void tma_issue_role(const TcArgs& args, uint8_t* smem_a, uint32_t bar_tma_full0, uint32_t bar_a_empty0, int first_tile, int end_tile) {
+__device__ void tma_issue_role(const TcArgs& args, uint8_t* smem_a, uint32_t bar_tma_full0, uint32_t bar_a_empty0, int first_tile, int tile_step, int end_tile) {
   const ConvParams& p = args.p;
   const TcPlan& t = args.t;
   WaitProf wprof; wprof.init(args.prof);
@@ -578,7 +578,7 @@ __device__ void tma_issue_role(const TcArgs& args, uint8_t* smem_a, uint32_t bar
   const uint32_t stage_tx = box_bytes * (uint32_t)t.planes * (p.stride == 2 ? 4u : 1u) * (p.resid != nullptr ? 2u : 1u);
   const int c8 = p.Cin >> 3;
   uint32_t sa = 0, pa = 0;
-  for (int tile = first_tile; tile < end_tile; ++tile) {
+  for (int tile = first_tile; tile < end_tile; tile += tile_step) {
     const TileCoord tc = decode_tile(t, tile);
     int u0, v0;
     tile_origin(p, tc, u0, v0);
@@ -639,7 +639,7 @@ __device__ __forceinline__ int pad_donor(int u, int extent, int pad_mode) {
 
 // MODE / HAS_RESID / SIDE as in produce_act16
 template <bool HAS_RESID, int MODE, bool SIDE>
-__device__ void transform_act16(const TcArgs& args, uint8_t* smem_a, float2* coeff, uint32_t bar_tma_full0, uint32_t bar_a_full0, int first_tile, int end_tile, int ptid) {
+__device__ void transform_act16(const TcArgs& args, uint8_t* smem_a, float2* coeff, uint32_t bar_tma_full0, uint32_t bar_a_full0, int first_tile, int tile_step, int end_tile, int ptid) {
   const ConvParams& p = args.p;
   const TcPlan& t = args.t;
   constexpr int PU = 4;
@@ -661,7 +661,7 @@ __device__ void transform_act16(const TcArgs& args, uint8_t* smem_a, float2* coe
   uint32_t sa = 0, pa = 0;
   int cur_n = -1;
   float sc[8], sh[8];
-  for (int tile = first_tile; tile < end_tile; ++tile) {
+  for (int tile = first_tile; tile < end_tile; tile += tile_step) {
     const TileCoord tc = decode_tile(t, tile);
     int u0, v0;
     tile_origin(p, tc, u0, v0);
@@ -729,21 +729,26 @@ __device__ void transform_act16(const TcArgs& args, uint8_t* smem_a, float2* coe
         }
       }
       if (border) {
+        // Out-of-image slots form a frame of `top` / `bot` rows and `left` / `right` columns around the in-image rectangle: only those are
+        // visited (one row or column of slots for a 3x3 layer), each taking its value from the mirrored / replicated in-image slot.
         named_bar_sync(1, PT);                 // every in-image slot of the stage is transformed
-        for (int blk = blk0; blk < nblk; blk += blk_step) {
-          const int q = blk * 8 + l8;
+        const int top = min(max(-u0, 0), t.halo_h), bot = min(max(u0 + t.halo_h - p.Hc, 0), t.halo_h - top);
+        const int left = min(max(-v0, 0), halo_w), right = min(max(v0 + halo_w - p.Wc, 0), halo_w - left);
+        const int n_rows = (top + bot) * halo_w, lr = left + right, n_oob = n_rows + (t.halo_h - top - bot) * lr;
+        for (int item = ptid; item < n_oob * planes; item += PT) {
+          const int gi = item % planes, idx = item / planes;
           int hy, hx;
-          if (!slot_rc(t, p.stride, q, inv_p, inv_sub, hy, hx)) continue;
-          const int u = u0 + hy, v = v0 + hx;
-          if (u >= 0 && u < p.Hc && v >= 0 && v < p.Wc) continue;
+          if (idx < n_rows) { const int r = idx / halo_w; hx = idx - r * halo_w; hy = r < top ? r : t.halo_h - bot + (r - top); }
+          else { const int j = idx - n_rows, r = j / lr, k = j - r * lr; hy = top + r; hx = k < left ? k : halo_w - right + (k - left); }
+          uint8_t* pl = smem_a + (size_t)sa * t.a_stage_bytes + (size_t)gi * t.a_plane_bytes;
           uint4 val = make_uint4(0u, 0u, 0u, 0u);
-          const int du = pad_donor(u, p.Hc, p.pad_mode), dv = pad_donor(v, p.Wc, p.pad_mode);
+          const int du = pad_donor(u0 + hy, p.Hc, p.pad_mode), dv = pad_donor(v0 + hx, p.Wc, p.pad_mode);
           if (du >= 0 && dv >= 0) {
             const int dy = du - u0, dx = dv - v0;
             if (dy < 0 || dy >= t.halo_h || dx < 0 || dx >= halo_w) continue;      // partial-tile overhang: nothing reads this slot
-            val = *reinterpret_cast<const uint4*>(plane + (size_t)rc_slot(t, p.stride, dy, dx) * 16);
+            val = *reinterpret_cast<const uint4*>(pl + (size_t)rc_slot(t, p.stride, dy, dx) * 16);
           } else if (p.pad_mode != PAD_ZERO) continue;
-          *reinterpret_cast<uint4*>(plane + (size_t)q * 16) = val;
+          *reinterpret_cast<uint4*>(pl + (size_t)rc_slot(t, p.stride, hy, hx) * 16) = val;
         }
       }
       fence_proxy_async_smem();       // generic-proxy smem writes -> visible to tcgen05.mma (async proxy)
@@ -951,8 +956,8 @@ __device__ __forceinline__ void transpose8x8(uint32_t (&r)[8], int l8) {
   }
 }
 
-__device__ __noinline__ void epilogue_swap(const TcArgs& args, uint32_t tmem_base, uint32_t acc_full0, uint32_t acc_empty0, int first_tile, int end_tile,
-                                           int quad, int lane) {
+__device__ __noinline__ void epilogue_swap(const TcArgs& args, uint32_t tmem_base, uint32_t acc_full0, uint32_t acc_empty0, int first_tile, int tile_step,
+                                           int end_tile, int quad, int lane, int eg, int EG) {
   const ConvParams& p = args.p;
   const TcPlan& t = args.t;
   const int co = quad * 32 + lane;                 // this thread's output channel = its TMEM lane
@@ -969,13 +974,13 @@ __device__ __noinline__ void epilogue_swap(const TcArgs& args, uint32_t tmem_bas
   int cur_n = -1;
   auto flush = [&]() {
     if (cur_n < 0) return;
-    double* st = p.out_part + (((size_t)blockIdx.x * p.N + cur_n) * p.Cout + co) * 2;
+    double* st = p.out_part + ((((size_t)blockIdx.x * EG + eg) * p.N + cur_n) * p.Cout + co) * 2;
     st[0] = sum_d; st[1] = sq_d;
     sum_d = 0.0; sq_d = 0.0;
   };
   WaitProf wprof; wprof.init(args.prof);
-  uint32_t it = 0;
-  for (int tile = first_tile; tile < ((t.dbg & 32) ? 0 : end_tile); ++tile, ++it) {
+  uint32_t it = (uint32_t)eg;
+  for (int tile = first_tile + eg * tile_step; tile < ((t.dbg & 32) ? 0 : end_tile); tile += EG * tile_step, it += EG) {
     const TileCoord tc = decode_tile(t, tile);
     if (tc.n != cur_n) { flush(); cur_n = tc.n; }
     const uint32_t buf = it & 1u;
@@ -1026,7 +1031,7 @@ __device__ __noinline__ void epilogue_swap(const TcArgs& args, uint32_t tmem_bas
     sum_d += (double)ts; sq_d += (double)tq;
   }
   flush();
-  wprof.flush(2, quad == (TC_FIRST_EPI_WARP & 3) && lane == 0);
+  wprof.flush(2, eg == 0 && quad == (TC_FIRST_EPI_WARP & 3) && lane == 0);
 }
 
 constexpr int NBARS = 3 * TC_MAX_A_STAGES + 2 * TC_MAX_B_STAGES + 4;     // A_FULL, A_EMPTY, B_FULL, B_EMPTY, ACC_FULL/EMPTY x2, TMA_FULL
@@ -1045,7 +1050,7 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
   uint32_t* ent_tab = tmem_slot + 4;                                         // [TC_MAX_ENT rounded to 84] tap offsets (MMA warp)
   int* srcpix = reinterpret_cast<int*>(ent_tab + 84);                       // [2][NPOS] source tables of the current / next tile (gather producers only)
   float2* coeff = reinterpret_cast<float2*>(srcpix + t.tbl_ints);             // [Cin] InstanceNorm (scale, shift) of sample n
-  float* fold_ring = reinterpret_cast<float*>(coeff + 256);                   // [256][TC_FOLD_PITCH] (fold_s layers) | double [4 warps][stat_ch][2] statistics
+  float* fold_ring0 = reinterpret_cast<float*>(coeff + 256);                   // [256][TC_FOLD_PITCH] (fold_s layers) | double [4 warps][stat_ch][2] statistics
 
   const uint32_t bar0 = smem_u32(bars);
   auto A_FULL = [&](int s) { return bar0 + 8u * (uint32_t)s; };
@@ -1058,6 +1063,9 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
+  const long long prof_c0 = args.prof ? clock64() : 0;
+  const unsigned long long prof_t0 = args.prof ? global_ns() : 0ull;
+  const int first_prod_warp = TC_FIRST_PROD_WARP + 4 * (t.epi_groups - 1);   // a second epilogue group takes warps 6-9 (TMA-fed layers only)
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < TC_MAX_A_STAGES; ++s) { mbar_init(A_FULL(s), (uint32_t)t.prod_warps * ARRIVALS_PER_WARP); mbar_init(A_EMPTY(s), 1); }
@@ -1074,9 +1082,13 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
 
   // Each CTA walks a contiguous run of tiles; tiles are numbered column-major inside a frame (decode_tile), so consecutive tiles
   // of a CTA are vertical neighbours (halo rows are shared, statistics are flushed once per frame run, L2 sees nearby rows).
-  const int first_tile = (int)((long long)blockIdx.x * t.num_tiles / gridDim.x);
-  const int end_tile = (int)((long long)(blockIdx.x + 1) * t.num_tiles / gridDim.x);
-  const int tile_step = 1;
+  // Tile -> CTA assignment (static, so the statistics' partial sums are reproducible).  rr_tiles: CTA b takes tiles b, b + grid, ...
+  // -- the tiles in flight at any moment are neighbours (their halos hit L2 together) and the expensive ones (image borders: a whole
+  // tile column at the left / right edge) spread evenly; with contiguous runs the CTAs that own a border column finish 20-35 % late
+  // (tcspan, tools/prof2.sh).  Otherwise: contiguous runs, column-major inside a frame.
+  const int first_tile = t.rr_tiles ? (int)blockIdx.x : (int)((long long)blockIdx.x * t.num_tiles / gridDim.x);
+  const int end_tile = t.rr_tiles ? t.num_tiles : (int)((long long)(blockIdx.x + 1) * t.num_tiles / gridDim.x);
+  const int tile_step = t.rr_tiles ? (int)gridDim.x : 1;
 
   if (warp == 0) {
     // =========================== weight loader ===========================
@@ -1132,22 +1144,29 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
     else if (t.nterms == 1 && t.k16_per_ent == 1 && t.MB == 2) mma_role<1, 2>(t, mc);
     else if (t.nterms == 1 && t.k16_per_ent == 1 && t.MB == 1) mma_role<1, 1>(t, mc);
     else mma_role<0, 0>(t, mc);
-  } else if (warp < TC_FIRST_PROD_WARP) {
+  } else if (warp < first_prod_warp) {
     // =========================== epilogue ===========================
+    // EG = 1: one group of four warps drains every tile.  EG = 2 (epilogue-bound TMA-fed layers): warps 2-5 drain the even tiles of
+    // the CTA's run (accumulator buffer 0), warps 6-9 the odd ones (buffer 1), each with its own scratch and named barriers.
+    const int EG = t.epi_groups, eg = (warp - TC_FIRST_EPI_WARP) >> 2;
+    const int ewarp = (warp - TC_FIRST_EPI_WARP) & 3;   // warp inside its group
     const int quad = warp & 3;                        // TMEM lane quadrant this warp may read
+    float* const fold_ring = fold_ring0 + (size_t)eg * (t.epi_scratch_bytes >> 2);
+    const int bar_a = 3 + 3 * eg, bar_b = 4 + 3 * eg, bar_c = 5 + 3 * eg;
     const int njc = t.NPAD >> 4;
     const int my_chan = ((lane & 16) ? 8 : 0) + ((lane & 8) ? 4 : 0) + ((lane & 4) ? 2 : 0) + ((lane & 2) ? 1 : 0);
     if (t.swap_ab) {
-      epilogue_swap(args, tmem_base, ACC_FULL(0), ACC_EMPTY(0), first_tile, end_tile, quad, lane);
+      epilogue_swap(args, tmem_base, ACC_FULL(0), ACC_EMPTY(0), first_tile, tile_step, end_tile, quad, lane, eg, EG);
     } else if (t.fold_s) {
       // Image layer with the horizontal taps folded into N:  TMEM holds T[m][s*3+co] = sum_{r,ci} in[m + r*P][ci] w[co][ci][r][s];
-      // out[m][co] = sum_s T[m + s][s*3 + co].  Rows are exchanged through a two-block ring in shared memory: block mb is
-      // written to half (mb & 1), then every thread finishes the output 8 rows behind its own TMEM row.
-      const int tid = quad * 32 + lane;             // TMEM lane (row of the M block) this thread reads
+      // out[m][co] = sum_s T[m + s][s*3 + co].  Rows are exchanged through a ring of 128 + 8 rows in shared memory (row R at
+      // slot R mod 136: block mb never overwrites the last 8 rows of block mb - 1), then every thread finishes the output 8 rows
+      // behind its own TMEM row.
+      const int tid = quad * 32 + lane;             // TMEM lane (row of the M block) this thread reads (= its slot of the group's ring)
       const float b0 = p.bias[0], b1 = p.bias[1], b2 = p.bias[2];
-      uint32_t it = 0;
+      uint32_t it = (uint32_t)eg;
       WaitProf wprof; wprof.init(args.prof);
-      for (int tile = first_tile; tile < ((t.dbg & 32) ? 0 : end_tile); tile += tile_step, ++it) {
+      for (int tile = first_tile + eg * tile_step; tile < ((t.dbg & 32) ? 0 : end_tile); tile += EG * tile_step, it += EG) {
         const TileCoord tc = decode_tile(t, tile);
         const uint32_t buf = it & 1u;
         mbar_wait_warp(ACC_FULL(buf), (it >> 1) & 1u, err, 5, wprof);
@@ -1158,13 +1177,13 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
           tmem_ld16(taddr, v0);
           tmem_ld16(taddr + 16u, v1);
           if (mb == t.MB - 1) { tc_fence_before(); mbar_arrive_warp(ACC_EMPTY(buf)); }
-          named_bar_sync(3, 128);                       // readers of the previous block are done with this half's neighbour rows
-          float* row = fold_ring + (size_t)((mb & 1) * 128 + tid) * TC_FOLD_PITCH;
+          named_bar_sync(bar_a, 128);                       // readers of the previous block are done with this half's neighbour rows
+          float* row = fold_ring + (size_t)((mb * 128 + tid) % TC_FOLD_ROWS) * TC_FOLD_PITCH;
 #pragma unroll
           for (int i = 0; i < 16; ++i) row[i] = v0[i];
 #pragma unroll
           for (int i = 0; i < 11; ++i) row[16 + i] = v1[i];
-          named_bar_sync(4, 128);
+          named_bar_sync(bar_b, 128);
           const int m = mb * 128 + tid - 8;
           if (m >= 0) {
             const int ty = m / t.P, tx = m - ty * t.P;
@@ -1174,7 +1193,7 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
 #pragma unroll
               for (int sx = 0; sx < 9; ++sx) {
                 const int mm = m + sx;
-                const float* rr = fold_ring + (size_t)(((mm >> 7) & 1) * 128 + (mm & 127)) * TC_FOLD_PITCH + sx * 3;
+                const float* rr = fold_ring + (size_t)(mm % TC_FOLD_ROWS) * TC_FOLD_PITCH + sx * 3;
                 a0 += rr[0]; a1 += rr[1]; a2 += rr[2];
               }
               store_image(p, tc.n, oy, ox, a0, a1, a2);
@@ -1189,30 +1208,30 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
       // stays well conditioned for |mean| >> sigma.  When the sample changes (and at the end) the four warps' sums are added in
       // a fixed order and written -- no atomics -- to this CTA's slot of the partial table; stats_finalize_kernel folds the CTAs
       // of a sample in index order, so the statistics (hence the whole forward) are bit-reproducible run to run.
-      double* wstat = reinterpret_cast<double*>(fold_ring) + (size_t)(warp - TC_FIRST_EPI_WARP) * t.stat_ch * 2;
+      double* wstat = reinterpret_cast<double*>(fold_ring) + (size_t)ewarp * t.stat_ch * 2;
       for (int c = lane; c < t.stat_ch * 2; c += 32) wstat[c] = 0.0;
       __syncwarp();
       int cur_n = -1;
-      const int etid = threadIdx.x - TC_FIRST_EPI_WARP * 32;
+      const int etid = ewarp * 32 + lane;
       auto flush = [&]() {
         if (cur_n < 0 || p.out_fmt != OUT_F32_NHWC_STATS) return;
-        named_bar_sync(5, 128);                 // every epilogue warp has added its last tile of sample cur_n
+        named_bar_sync(bar_c, 128);             // every warp of the group has added its last tile of sample cur_n
         double* all = reinterpret_cast<double*>(fold_ring);
         for (int c = etid; c < p.co_pass; c += 128) {
           double s1 = 0.0, s2 = 0.0;
 #pragma unroll
           for (int w = 0; w < 4; ++w) { s1 += all[((size_t)w * t.stat_ch + c) * 2]; s2 += all[((size_t)w * t.stat_ch + c) * 2 + 1]; }
-          double* st = p.out_part + (((size_t)blockIdx.x * p.N + cur_n) * p.Cout + p.co_off + c) * 2;
+          double* st = p.out_part + ((((size_t)blockIdx.x * EG + eg) * p.N + cur_n) * p.Cout + p.co_off + c) * 2;
           st[0] = s1; st[1] = s2;
 #pragma unroll
           for (int w = 0; w < 4; ++w) { all[((size_t)w * t.stat_ch + c) * 2] = 0.0; all[((size_t)w * t.stat_ch + c) * 2 + 1] = 0.0; }
         }
-        named_bar_sync(5, 128);
+        named_bar_sync(bar_c, 128);
       };
       const float inv_p = 1.0f / (float)t.P;
-      uint32_t it = 0;
+      uint32_t it = (uint32_t)eg;
       WaitProf wprof; wprof.init(args.prof);
-      for (int tile = first_tile; tile < ((t.dbg & 32) ? 0 : end_tile); tile += tile_step, ++it) {
+      for (int tile = first_tile + eg * tile_step; tile < ((t.dbg & 32) ? 0 : end_tile); tile += EG * tile_step, it += EG) {
         const TileCoord tc = decode_tile(t, tile);
         if (tc.n != cur_n) { flush(); cur_n = tc.n; }
         const uint32_t buf = it & 1u;
@@ -1329,12 +1348,12 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
   } else if (t.tma_mode) {
     // =========================== TMA-fed operand path ===========================
     if (warp == TC_FIRST_PROD_WARP + TC_PROD_WARPS - 1) {
-      if (lane == 0) tma_issue_role(args, smem_a, TMA_FULL(0), A_EMPTY(0), first_tile, end_tile);
-    } else if (warp < TC_FIRST_PROD_WARP + t.prod_warps) {
-      const int ptid = threadIdx.x - TC_FIRST_PROD_WARP * 32;
+      if (lane == 0) tma_issue_role(args, smem_a, TMA_FULL(0), A_EMPTY(0), first_tile, tile_step, end_tile);
+    } else if (warp < first_prod_warp + t.prod_warps) {
+      const int ptid = threadIdx.x - first_prod_warp * 32;
       const bool has_resid = p.resid != nullptr;
-#define NST_XFORM(R, M) do { if (p.side_out != nullptr) transform_act16<R, M, true>(args, smem_a, coeff, TMA_FULL(0), A_FULL(0), first_tile, end_tile, ptid); \
-                             else transform_act16<R, M, false>(args, smem_a, coeff, TMA_FULL(0), A_FULL(0), first_tile, end_tile, ptid); } while (0)
+#define NST_XFORM(R, M) do { if (p.side_out != nullptr) transform_act16<R, M, true>(args, smem_a, coeff, TMA_FULL(0), A_FULL(0), first_tile, tile_step, end_tile, ptid); \
+                             else transform_act16<R, M, false>(args, smem_a, coeff, TMA_FULL(0), A_FULL(0), first_tile, tile_step, end_tile, ptid); } while (0)
       if (has_resid) {
         if (!p.pre_relu && !p.post_relu) NST_XFORM(true, 1);
         else if (!p.pre_relu) NST_XFORM(true, 2);
@@ -1565,6 +1584,16 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
   if (warp == 1) {
     tc_fence_after();
     tmem_dealloc(tmem_base, 512);
+  }
+  if (args.prof != nullptr && threadIdx.x == 0) {
+    if (blockIdx.x == 0) {                                                  // debug: effective SM clock of this launch = cycles / ns
+      atomicAdd(args.prof + 14, (unsigned long long)(clock64() - prof_c0));
+      atomicAdd(args.prof + 15, (unsigned long long)(global_ns() - prof_t0));
+    }
+    if (args.prof_cta != nullptr) {                                         // per-CTA wall-clock span (launch skew / tail analysis)
+      args.prof_cta[2 * blockIdx.x] = prof_t0;
+      args.prof_cta[2 * blockIdx.x + 1] = global_ns();
+    }
   }
 }
 

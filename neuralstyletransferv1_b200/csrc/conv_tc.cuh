@@ -16,7 +16,8 @@ constexpr int TC_MAX_A_STAGES = 4;
 constexpr int TC_MAX_B_STAGES = 8;
 constexpr int TC_SMEM_LIMIT = 227 * 1024;
 constexpr int TC_FOLD_PITCH = 29;      // floats per ring row (27 used; odd pitch = conflict-free)
-constexpr int TC_FOLD_RING_BYTES = 256 * TC_FOLD_PITCH * 4;
+constexpr int TC_FOLD_ROWS = 136;      // one M block + the 8 rows of the previous block its first outputs still read
+constexpr int TC_FOLD_RING_BYTES = TC_FOLD_ROWS * TC_FOLD_PITCH * 4;
 
 // GEMM view of one layer:  D[m, co] = sum_{entry e, k} A[m + ent_off[e], k] * W[e][k][co]
 //   m      : flat position inside the CTA tile's halo buffer (pitch P), M = MB*128 rows
@@ -38,6 +39,10 @@ struct TcPlan {
   int tg, ngroups;          // entries per weight stage, stages per chunk
   int a_stages, b_stages;
   int prod_warps;           // operand-producer warps that take part (the rest of TC_PROD_WARPS exit at once)
+  int rr_tiles;             // CTA b takes tiles b, b + grid, b + 2*grid, ... instead of one contiguous run
+  int epi_groups;           // 1, or 2 on epilogue-bound TMA-fed layers: warps 6-9 form a second epilogue group that drains the odd tiles of
+                            // the CTA's run (accumulator buffer 1) while warps 2-5 drain the even ones; the transform then has <= 5 warps
+  uint32_t epi_scratch_bytes;   // shared-memory scratch of ONE epilogue group (fold ring, or per-warp double channel statistics)
   int b_resident;           // the layer's whole weight set fits the B ring: load every stage once, never recycle
   int nterms;               // 1, or 3 (hi*hi + lo*hi + hi*lo)
   int a_tplanes, b_tplanes; // operand planes kept (1, or 2 = hi and lo)
@@ -78,6 +83,7 @@ struct TcArgs {
   TcPlan t;
   const void* wpack;        // [chunk][group][term][entry in group][plane][NPAD][8] 16-bit
   unsigned int* err_flag;   // set non-zero when a pipeline wait times out
+  unsigned long long* prof_cta;   // debug: [grid][2] globaltimer at kernel entry / exit of every CTA, or null
   unsigned long long* prof; // debug (NST_TC_PROF=1): [code 1..6] cycles waited per barrier kind, [8+role] role cycles; or null
 };
 

@@ -122,30 +122,48 @@ struct StatsFinalizeArgs {
   const float* gamma;       // [C]
   const float* beta;        // [C]
   float2* coeff;            // [N][C]
-  int parts, N, C;
-  int tiles_per_img;        // tiles of one sample; CTA b owns tiles [b*T/parts, (b+1)*T/parts), T = N * tiles_per_img
+  int rr;                   // tile -> CTA assignment of the producing launch: 1 = CTA b takes tiles b, b + parts, ...; 0 = contiguous runs
+  int parts, groups, N, C;  // part table [parts * groups][N][C][2]: slot (CTA b, epilogue group g) = b * groups + g
+  int tiles_per_img;        // tiles of one sample; CTA b owns tiles [b*T/parts, (b+1)*T/parts), T = N * tiles_per_img; its group g drains
+                            // the tiles at odd/even offsets from the start of that run (offset % groups == g)
   double inv_count;         // 1 / (H*W)
 };
 
+// One warp per (n, c): lane l adds the slots of CTAs l, l + 32, ... in index order, then a fixed butterfly joins the 32 lanes -- the
+// summation tree depends only on (parts, groups), never on scheduling.
 __global__ void __launch_bounds__(128) stats_finalize_kernel(const __grid_constant__ StatsFinalizeArgs a) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int i = (int)((blockIdx.x * blockDim.x + threadIdx.x) >> 5), lane = threadIdx.x & 31;
   if (i >= a.N * a.C) return;
   const int n = i / a.C, c = i - n * a.C;
   double s1 = 0.0, s2 = 0.0;
-  if (a.parts == 1) {
-    const double* st = a.part + ((size_t)n * a.C + c) * 2;
-    s1 = st[0]; s2 = st[1];
+  if (a.parts == 1 && a.groups == 1) {
+    if (lane == 0) { const double* st = a.part + ((size_t)n * a.C + c) * 2; s1 = st[0]; s2 = st[1]; }
   } else {
-    const long long T = (long long)a.N * a.tiles_per_img;
-    const long long lo = (long long)n * a.tiles_per_img, hi = lo + a.tiles_per_img;
-    for (int b = 0; b < a.parts; ++b) {
-      const long long t0 = (long long)b * T / a.parts, t1 = (long long)(b + 1) * T / a.parts;
-      if (t0 >= hi) break;
-      if (t1 <= lo || t0 == t1) continue;
-      const double* st = a.part + (((size_t)b * a.N + n) * a.C + c) * 2;
-      s1 += st[0]; s2 += st[1];
+    const int T = a.N * a.tiles_per_img, lo = n * a.tiles_per_img, hi = lo + a.tiles_per_img;
+    for (int b = lane; b < a.parts; b += 32) {
+      int from, to;                        // [from, to): indices i of CTA b's tile sequence that fall into sample n
+      if (a.rr) {                          // CTA b drains tiles b + i * parts
+        from = lo > b ? (lo - b + a.parts - 1) / a.parts : 0;
+        to = hi > b ? (hi - b + a.parts - 1) / a.parts : 0;
+      } else {                             // CTA b drains tiles [b*T/parts, (b+1)*T/parts)
+        const int t0 = (int)((long long)b * T / a.parts), t1 = (int)((long long)(b + 1) * T / a.parts);
+        from = (lo > t0 ? lo : t0) - t0;
+        to = (hi < t1 ? hi : t1) - t0;
+      }
+      for (int g = 0; g < a.groups; ++g) { // epilogue group g drains the indices with i % groups == g
+        const int first = from + ((g - from) % a.groups + a.groups) % a.groups;
+        if (first >= to) continue;         // that group never saw sample n: slot unwritten
+        const double* st = a.part + ((((size_t)b * a.groups + g) * a.N + n) * a.C + c) * 2;
+        s1 += st[0]; s2 += st[1];
+      }
     }
   }
+#pragma unroll
+  for (int off = 16; off >= 1; off >>= 1) {
+    s1 += __shfl_xor_sync(0xffffffffu, s1, off);
+    s2 += __shfl_xor_sync(0xffffffffu, s2, off);
+  }
+  if (lane != 0) return;
   const double mean = s1 * a.inv_count;
   double var = s2 * a.inv_count - mean * mean;
   if (var < 0.0) var = 0.0;
@@ -154,12 +172,12 @@ __global__ void __launch_bounds__(128) stats_finalize_kernel(const __grid_consta
   a.coeff[i] = make_float2(scale, a.beta[c] - (float)mean * scale);
 }
 
-cudaError_t launch_stats_finalize(const double* part, int parts, int N, int C, int tiles_per_img, double inv_count,
+cudaError_t launch_stats_finalize(const double* part, int parts, int groups, int rr, int N, int C, int tiles_per_img, double inv_count,
                                   const float* gamma, const float* beta, float2* coeff, cudaStream_t stream) {
   StatsFinalizeArgs a;
   a.part = part; a.gamma = gamma; a.beta = beta; a.coeff = coeff;
-  a.parts = parts; a.N = N; a.C = C; a.tiles_per_img = tiles_per_img; a.inv_count = inv_count;
-  stats_finalize_kernel<<<(N * C + 127) / 128, 128, 0, stream>>>(a);
+  a.parts = parts; a.groups = groups; a.rr = rr; a.N = N; a.C = C; a.tiles_per_img = tiles_per_img; a.inv_count = inv_count;
+  stats_finalize_kernel<<<(N * C + 3) / 4, 128, 0, stream>>>(a);
   return cudaGetLastError();
 }
 

@@ -29,7 +29,7 @@ struct CompositeArgs {
   float w[COMP_MAX_R * COMP_MAX_J];
 };
 cudaError_t launch_composite(const CompositeArgs& a, bool u8, cudaStream_t stream);
-cudaError_t launch_stats_finalize(const double* part, int parts, int N, int C, int tiles_per_img, double inv_count,
+cudaError_t launch_stats_finalize(const double* part, int parts, int groups, int rr, int N, int C, int tiles_per_img, double inv_count,
                                   const float* gamma, const float* beta, float2* coeff, cudaStream_t stream);
 }  // namespace nst
 
@@ -418,7 +418,8 @@ static bool tc_layout(const ConvParams& p, TcPlan& t, int MB, int bTH, int bTW, 
   // + per-sample norm coefficients [Cin<=256] + epilogue scratch: fold ring, or per-warp double channel statistics
   t.tbl_ints = tma ? 0 : 2 * (int)round_up((size_t)t.NPOS, 4);
   t.stat_ch = (int)round_up((size_t)(t.phase_mode ? t.NPAD / 4 : t.NPAD), 16);
-  const int bar_bytes = 704 + t.tbl_ints * 4 + 256 * 8 + (t.fold_s ? TC_FOLD_RING_BYTES : 4 * t.stat_ch * 16);
+  t.epi_scratch_bytes = (uint32_t)(t.fold_s ? TC_FOLD_RING_BYTES : 4 * t.stat_ch * 16);
+  const int bar_bytes = 704 + t.tbl_ints * 4 + 256 * 8 + t.epi_groups * (int)t.epi_scratch_bytes;
   const int avail = TC_SMEM_LIMIT - b_total - bar_bytes;
   const int a_stages = avail / (int)t.a_stage_bytes;
   const int want = t.nchunks == 1 ? 2 : 3;
@@ -587,7 +588,7 @@ extern "C" int nst_create(int device, int arch, int precision, nst_handle** out)
   *h->err_host = 0;
   e = cudaHostGetDevicePointer((void**)&h->err_dev, h->err_host, 0);
   if (e == cudaSuccess) e = conv_tc_init();
-  if (e == cudaSuccess && getenv("NST_TC_PROF") && atoi(getenv("NST_TC_PROF"))) e = cudaMalloc((void**)&h->prof_dev, 16 * sizeof(unsigned long long));
+  if (e == cudaSuccess && getenv("NST_TC_PROF") && atoi(getenv("NST_TC_PROF"))) e = cudaMalloc((void**)&h->prof_dev, (64 * 16 + 64 * 2 * 148) * sizeof(unsigned long long));
   if (e != cudaSuccess) { cudaFreeHost(h->err_host); delete h; return fail(NST_ERR_CUDA, "nst_create: %s", cudaGetErrorString(e)); }
   *out = h;
   return NST_OK;
@@ -757,6 +758,18 @@ static bool tma_eligible(const ConvParams& q, const TcPlan& t, int in16) {
   return true;
 }
 
+// Epilogue groups of a TMA-fed layer.  tcprof (profiles/r02_tcprof_*): on the stride-2 32->64 layer, the Cin <= 96 sub-pixel layers and
+// the folded image layer the MMA warp waits 20-50 % of its time for a free accumulator while the transform warps idle > 50 %, so
+// four of them become a second epilogue group; everywhere else the transform needs its warps.  NST_EPI2_MASK=<layer bitmask> overrides.
+static int epi_groups_for(const LayerSpec& s, const TcPlan& t, int li) {
+  if (const char* e = getenv("NST_EPI2_MASK")) return ((strtoull(e, nullptr, 0) >> li) & 1ull) ? 2 : 1;
+  if (t.swap_ab || s.resid >= 0) return 1;
+  if (t.fold_s) return 2;
+  if (t.phase_mode) return s.cin <= 96 ? 2 : 1;
+  if (s.stride == 2) return 2;
+  return 1;
+}
+
 static int make_plan(nst_handle* h, int N, int H, int W) {
   if (N < 1 || H < 1 || W < 1) return fail(NST_ERR_INVALID, "bad shape N=%d H=%d W=%d", N, H, W);
   if (h->arch == NST_ARCH_NST && (H <= 40 || W <= 40))
@@ -867,12 +880,19 @@ static int make_plan(nst_handle* h, int N, int H, int W) {
       }
       q.resid = s.resid >= 0 ? (const void*)1 : nullptr;                   // plan-time flag (operand stage holds a residual tile too)
       lp.t.tma_mode = tma_eligible(q, lp.t, lp.in16) ? 1 : 0;
-      if (lp.t.tma_mode) lp.t.prod_warps = std::min(lp.t.prod_warps, TC_PROD_WARPS - 1);
+      lp.t.rr_tiles = getenv("NST_NO_RR") ? 0 : 1;
+      lp.t.epi_groups = 1;
+      if (lp.t.tma_mode) {
+        lp.t.epi_groups = epi_groups_for(s, lp.t, (int)li);
+        lp.t.prod_warps = std::min(lp.t.prod_warps, lp.t.epi_groups == 2 ? TC_PROD_WARPS - 5 : TC_PROD_WARPS - 1);
+      }
       bool ok = tc_plan_geometry(q, lp.t, fTH, fMB);
       if (!ok && lp.t.tma_mode) {                                            // shapes the TMA boxes cannot express fall back to the gather producers
         const int swap = lp.t.swap_ab;
         lp.t = h->dev[li].tc_static;
         lp.t.swap_ab = swap;
+        lp.t.epi_groups = 1;
+        lp.t.rr_tiles = getenv("NST_NO_RR") ? 0 : 1;
         ok = tc_plan_geometry(q, lp.t, fTH, fMB);
       }
       q.resid = nullptr;
@@ -886,7 +906,7 @@ static int make_plan(nst_handle* h, int N, int H, int W) {
                   s.cout, s.ks, s.stride);
     }
     if (s.out != BUF_IMAGE) {
-      lp.parts = lp.use_tc ? h->num_sms : 1;
+      lp.parts = lp.use_tc ? h->num_sms * 2 : 1;                    // (CTA, epilogue group) slots
       lp.part_off = stats_off;
       stats_off += round_up((size_t)lp.parts * nb * s.cout * 2 * sizeof(double), 256);
       lp.coeff_off = stats_off;
@@ -975,6 +995,31 @@ static int encode_layer_maps(LayerPlan& lp, const ConvParams& p, const void* src
   return NST_OK;
 }
 
+static void print_tcprof(nst_handle* h, int n_frames) {
+  std::vector<unsigned long long> all(64 * 16 + 64 * 2 * 148);
+  if (cudaMemcpy(all.data(), h->prof_dev, all.size() * sizeof(unsigned long long), cudaMemcpyDeviceToHost) != cudaSuccess) return;
+  for (size_t li = 0; li < h->specs.size() && li < 64; ++li) {
+    const LayerPlan& lp = h->plans[li];
+    if (!lp.use_tc) continue;
+    const unsigned long long* pc = all.data() + li * 16;
+    const int tiles = lp.t.tiles_x * lp.t.tiles_y * n_frames;
+    const double g = std::min(tiles, h->num_sms) * (double)h->dev[li].nsplit;
+    const double mhz = pc[15] ? 1e3 * (double)pc[14] / (double)pc[15] : 0.0;                  // CTA 0: SM cycles / ns
+    fprintf(stderr, "[tcprof] %-12s %s%s EG=%d tiles=%d | %.0f MHz | per-CTA kcycles: loader total %.0f wait B_EMPTY %.0f | mma total %.0f wait ACC_EMPTY %.0f A_FULL %.0f B_FULL %.0f | "
+                    "epi total %.0f wait ACC_FULL %.0f | prod total %.0f wait A_EMPTY %.0f | tma-issue total %.0f, transform waits TMA_FULL %.0f\n",
+            h->specs[li].name.c_str(), lp.t.tma_mode ? "tma" : "gather", lp.t.swap_ab ? "/T" : "", lp.t.epi_groups, tiles, mhz,
+            pc[8] / g / 1e3, pc[1] / g / 1e3, pc[9] / g / 1e3, pc[2] / g / 1e3, pc[3] / g / 1e3, pc[4] / g / 1e3, pc[10] / g / 1e3, pc[5] / g / 1e3,
+            pc[11] / g / 1e3, pc[6] / g / 1e3, pc[12] / g / 1e3, pc[7] / g / 1e3);
+    // wall-clock spans of the CTAs (last micro-batch, last split launch): start skew, mean busy span, tail
+    const unsigned long long* ct = all.data() + 64 * 16 + li * 2 * 148;
+    const int ctas = std::min(tiles, h->num_sms);
+    unsigned long long s0 = ~0ull, s1 = 0, e0 = ~0ull, e1 = 0; double span = 0;
+    for (int b = 0; b < ctas; ++b) { s0 = std::min(s0, ct[2 * b]); s1 = std::max(s1, ct[2 * b]); e0 = std::min(e0, ct[2 * b + 1]); e1 = std::max(e1, ct[2 * b + 1]); span += (double)(ct[2 * b + 1] - ct[2 * b]); }
+    fprintf(stderr, "[tcspan] %-12s kernel %.1f us = first start .. last end | starts spread %.1f us | CTA span mean %.1f us | first end at %.1f us\n",
+            h->specs[li].name.c_str(), (e1 - s0) / 1e3, (s1 - s0) / 1e3, span / ctas / 1e3, (e0 - s0) / 1e3);
+  }
+}
+
 static int run_forward(nst_handle* h, const IoSpec& io, int N, int H, int W, void* workspace, size_t workspace_bytes,
                        cudaStream_t stream, float* layer_ms) {
   if (h == nullptr) return fail(NST_ERR_INVALID, "forward: null handle");
@@ -1001,6 +1046,7 @@ static int run_forward(nst_handle* h, const IoSpec& io, int N, int H, int W, voi
     for (size_t i = 0; i < h->specs.size(); ++i) layer_ms[i] = 0.f;
   }
   auto buf = [&](int b) -> void* { return act + h->bufs[b].off * nb; };
+  if (layer_ms && h->prof_dev) CUDA_TRY(cudaMemsetAsync(h->prof_dev, 0, (64 * 16 + 64 * 2 * 148) * sizeof(unsigned long long), stream));
   for (int n0 = 0; n0 < N; n0 += nb) {
     const int n = std::min(nb, N - n0);
     if (layer_ms) CUDA_TRY(cudaEventRecord(ev[0], stream));
@@ -1039,7 +1085,7 @@ static int run_forward(nst_handle* h, const IoSpec& io, int N, int H, int W, voi
         p.out = buf(s.out);
         p.out_part = (double*)(stats + lp.part_off);
       }
-      int parts = 1, tiles_per_img = 0;
+      int parts = 1, groups = 1, tiles_per_img = 0;
       if (lp.use_tc) {
         TcArgs a;
         a.p = p; a.t = lp.t;
@@ -1056,25 +1102,15 @@ static int run_forward(nst_handle* h, const IoSpec& io, int N, int H, int W, voi
           memset(a.tmap, 0, sizeof(a.tmap)); memset(&a.tmap_res, 0, sizeof(a.tmap_res));
         }
         parts = conv_tc_grid(a.t, a.t.num_tiles, h->num_sms);
+        groups = lp.t.epi_groups;
         tiles_per_img = lp.t.tiles_x * lp.t.tiles_y;
         for (int part = 0; part < d.nsplit; ++part) {
         a.wpack = part == 0 ? d.wpack : d.wpack2;
         a.p.co_off = part * a.p.co_pass;
-        a.prof = layer_ms ? h->prof_dev : nullptr;
-        if (a.prof) CUDA_TRY(cudaMemsetAsync(a.prof, 0, 16 * sizeof(unsigned long long), stream));
-        CUDA_TRY(launch_conv_tc(a, h->num_sms, stream));
+        a.prof = (layer_ms && h->prof_dev && li < 64) ? h->prof_dev + li * 16 : nullptr;
+        a.prof_cta = (a.prof && h->num_sms <= 148) ? h->prof_dev + 64 * 16 + li * 2 * 148 : nullptr;      // read back after the whole forward: no
+        CUDA_TRY(launch_conv_tc(a, h->num_sms, stream));                                      // per-layer synchronisation, clocks stay in steady state
         if (part + 1 < d.nsplit) ++h->launches;
-        }
-        if (a.prof) {
-          unsigned long long pc[16];
-          CUDA_TRY(cudaMemcpyAsync(pc, a.prof, sizeof(pc), cudaMemcpyDeviceToHost, stream));
-          CUDA_TRY(cudaStreamSynchronize(stream));
-          const double g = std::min(a.t.num_tiles, h->num_sms);
-          fprintf(stderr, "[tcprof] %-12s %s tiles=%d ctas=%.0f | per-CTA kcycles: loader total %.0f wait B_EMPTY %.0f | mma total %.0f wait ACC_EMPTY %.0f A_FULL %.0f B_FULL %.0f | "
-                          "epi total %.0f wait ACC_FULL %.0f | prod total %.0f wait A_EMPTY %.0f | tma-issue total %.0f, transform waits TMA_FULL %.0f | epi-T TMEM-load wait %.0f\n", s.name.c_str(),
-                  lp.t.tma_mode ? "tma" : "gather", a.t.num_tiles, g,
-                  pc[8] / g / 1e3, pc[1] / g / 1e3, pc[9] / g / 1e3, pc[2] / g / 1e3, pc[3] / g / 1e3, pc[4] / g / 1e3, pc[10] / g / 1e3, pc[5] / g / 1e3,
-                  pc[11] / g / 1e3, pc[6] / g / 1e3, pc[12] / g / 1e3, pc[7] / g / 1e3, pc[13] / g / 1e3);
         }
       } else {
         if (s.out != BUF_IMAGE) CUDA_TRY(cudaMemsetAsync(p.out_part, 0, (size_t)n * s.cout * 2 * sizeof(double), stream));
@@ -1085,7 +1121,7 @@ static int run_forward(nst_handle* h, const IoSpec& io, int N, int H, int W, voi
         // fold the per-CTA partial statistics into the (scale, shift) the consumer applies (its gamma / beta belong to the norm in between)
         if (lp.consumer < 0) return fail(NST_ERR_STATE, "internal: layer %s has no consumer", s.name.c_str());
         const LayerDev& cd = h->dev[lp.consumer];
-        CUDA_TRY(launch_stats_finalize(p.out_part, parts, n, s.cout, tiles_per_img, 1.0 / ((double)lp.out_H * lp.out_W), cd.in_gamma, cd.in_beta,
+        CUDA_TRY(launch_stats_finalize(p.out_part, parts, groups, lp.use_tc ? lp.t.rr_tiles : 0, n, s.cout, tiles_per_img, 1.0 / ((double)lp.out_H * lp.out_W), cd.in_gamma, cd.in_beta,
                                        (float2*)(stats + lp.coeff_off), stream));
         ++h->launches;
       }
@@ -1101,6 +1137,7 @@ static int run_forward(nst_handle* h, const IoSpec& io, int N, int H, int W, voi
     }
   }
   if (layer_ms) for (auto& e : ev) cudaEventDestroy(e);
+  if (layer_ms && h->prof_dev) print_tcprof(h, std::min(N, nb));
   return NST_OK;
 }
 
@@ -1236,10 +1273,10 @@ extern "C" int nst_describe_plan(int arch, int precision, int N, int H, int W, c
     if (lp.use_tc) {
       const double useful = (double)lp.p.Ho * lp.p.Wo / ((double)t.tiles_x * t.tiles_y * t.MB * 128);
       snprintf(line, sizeof(line),
-               "%-28s %3d->%3d k%d s%d %4dx%-4d -> %4dx%-4d tc %s%s TH=%2d TW=%3d P=%3d MB=%d NPOS=%4d CK=%2d chunks=%d ent=%2d tg=%d "
+               "%-28s %3d->%3d k%d s%d %4dx%-4d -> %4dx%-4d tc %s%s EG=%d PW=%d TH=%2d TW=%3d P=%3d MB=%d NPOS=%4d CK=%2d chunks=%d ent=%2d tg=%d "
                "A=%dx%uB B=%dx%uB smem=%uB tiles/img=%d rows_useful=%.2f GF=%.2f\n",
                sp.name.c_str(), sp.cin, sp.cout, sp.ks, sp.stride, lp.p.Hs, lp.p.Ws, lp.p.Ho, lp.p.Wo, t.tma_mode ? (t.swap_ab ? "tma/T " : "tma   ") : (t.swap_ab ? "gath/T" : "gather"),
-               h.dev[li].prec == NST_PREC_F16X3 ? " x3" : (lp.out16 ? "" : " f32"), t.TH, t.TW, t.P, t.MB, t.NPOS,
+               h.dev[li].prec == NST_PREC_F16X3 ? " x3" : (lp.out16 ? "" : " f32"), t.epi_groups, t.prod_warps, t.TH, t.TW, t.P, t.MB, t.NPOS,
                t.CK, t.nchunks, t.nent, t.tg, t.a_stages, t.a_stage_bytes, t.b_stages, t.b_stage_bytes, t.smem_bytes,
                t.tiles_x * t.tiles_y, useful, lp.flops * 1e-9);
     } else {
