@@ -168,6 +168,15 @@ __device__ __forceinline__ void tma_load_4d(uint32_t dst_smem, const CUtensorMap
                ::"r"(dst_smem), "l"(tmap), "r"(0), "r"(c1), "r"(c2), "r"(c3), "r"(bar)
                : "memory");
 }
+// same box through a "wide" map: 3-D {2*W 8-byte elements, H, planes}; c1 is the first slot column
+__device__ __forceinline__ void tma_load_3d_wide(uint32_t dst_smem, const CUtensorMap* tmap, int c1, int c2, int c3, uint32_t bar) {
+  asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
+               ::"r"(dst_smem), "l"(tmap), "r"(2 * c1), "r"(c2), "r"(c3), "r"(bar)
+               : "memory");
+}
+__device__ __forceinline__ void tma_load_act(bool wide, uint32_t dst_smem, const CUtensorMap* tmap, int c1, int c2, int c3, uint32_t bar) {
+  if (wide) tma_load_3d_wide(dst_smem, tmap, c1, c2, c3, bar); else tma_load_4d(dst_smem, tmap, c1, c2, c3, bar);
+}
 __device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* tmap) {
   asm volatile("prefetch.tensormap [%0];" ::"l"(tmap) : "memory");
 }
@@ -577,6 +586,7 @@ __device__ void tma_issue_role(const TcArgs& args, uint8_t* smem_a, uint32_t bar
   const uint32_t box_bytes = (uint32_t)t.tma_rows * (uint32_t)t.P * 16u;
   const uint32_t stage_tx = box_bytes * (uint32_t)t.planes * (p.stride == 2 ? 4u : 1u) * (p.resid != nullptr ? 2u : 1u);
   const int c8 = p.Cin >> 3;
+  const bool wide = t.tma_wide != 0;
   uint32_t sa = 0, pa = 0;
   for (int tile = first_tile; tile < end_tile; tile += tile_step) {
     const TileCoord tc = decode_tile(t, tile);
@@ -591,15 +601,15 @@ __device__ void tma_issue_role(const TcArgs& args, uint8_t* smem_a, uint32_t bar
       for (int g = 0; g < t.planes; ++g) {
         const uint32_t dst = stage + (uint32_t)g * t.a_plane_bytes;
         if (p.stride == 1) {
-          tma_load_4d(dst, &args.tmap[0], v0, u0, plane0 + g, full);
-          if (p.resid != nullptr) tma_load_4d(dst + t.a_res_off, &args.tmap_res, v0, u0, plane0 + g, full);
+          tma_load_act(wide, dst, &args.tmap[0], v0, u0, plane0 + g, full);
+          if (p.resid != nullptr) tma_load_act(wide, dst + t.a_res_off, &args.tmap_res, v0, u0, plane0 + g, full);
         } else {
 #pragma unroll
           for (int sub = 0; sub < 4; ++sub) {
             // halo slot (2i + py, 2j + px) is conv-space (u0 + py + 2i, v0 + px + 2j): row i / column j of the parity view
             // ((u0 + py) & 1, (v0 + px) & 1) starting at floor((u0 + py) / 2), floor((v0 + px) / 2)  (>> is arithmetic)
             const int uu = u0 + (sub >> 1), vv = v0 + (sub & 1);
-            tma_load_4d(dst + (uint32_t)(sub * t.SUBPOS) * 16u, &args.tmap[((uu & 1) << 1) | (vv & 1)], vv >> 1, uu >> 1, plane0 + g, full);
+            tma_load_act(wide, dst + (uint32_t)(sub * t.SUBPOS) * 16u, &args.tmap[((uu & 1) << 1) | (vv & 1)], vv >> 1, uu >> 1, plane0 + g, full);
           }
         }
       }
@@ -661,6 +671,29 @@ __device__ void transform_act16(const TcArgs& args, uint8_t* smem_a, float2* coe
   uint32_t sa = 0, pa = 0;
   int cur_n = -1;
   float sc[8], sh[8];
+  // (The residual operand is staged by TMA next to the source tile.  Reading it from HBM in the transform instead -- registers, one loop
+  // iteration ahead -- was 30 % slower: the ~2 us load latency under load needs a prefetch distance of whole stages, which only the
+  // shared-memory ring provides.)
+  const int nit = ((nblk + blk_step - 1) / blk_step + PU - 1) / PU;      // loop iterations per (tile, chunk), the same for every thread
+  // The slots a thread visits are the same in every tile: their in-plane offset hy * Ws + hx and whether they are tile-interior
+  // (side output) are computed once (the planner keeps nit <= RIT for layers with a residual operand or a side output).
+  constexpr int RIT = 2;
+  int soff[RIT][PU];
+  uint32_t live_m = 0u, inner_m = 0u;
+  if (SIDE) {
+#pragma unroll
+    for (int it = 0; it < RIT; ++it)
+#pragma unroll
+      for (int u = 0; u < PU; ++u) {
+        const int blk = blk0 + (it * PU + u) * blk_step;
+        const int q = blk * 8 + l8;
+        const int hy = (int)(((float)q + 0.5f) * inv_p), hx = q - hy * kP;
+        soff[it][u] = hy * kWs + hx;
+        if (blk < nblk) live_m |= 1u << (it * PU + u);
+        const int iy = hy - kPadT, ix = hx - kPadL;
+        if ((iy >= 0) & (iy < kTH) & (ix >= 0) & (ix < kTW)) inner_m |= 1u << (it * PU + u);
+      }
+  }
   for (int tile = first_tile; tile < end_tile; tile += tile_step) {
     const TileCoord tc = decode_tile(t, tile);
     int u0, v0;
@@ -687,7 +720,9 @@ __device__ void transform_act16(const TcArgs& args, uint8_t* smem_a, float2* coe
       const uint8_t* rplane = plane + t.a_res_off;
       // side output: slot (hy, hx) of plane (n, ch*planes + g) is source pixel (u0 + hy, v0 + hx) (identity-mapped stride-1 layers)
       const long long side_base = SIDE ? (((long long)tc.n * (p.Cin >> 3) + (ch * planes + g)) * p.Hs + u0) * p.Ws + v0 : 0;   // in slots; may be < 0
-      for (int blk = blk0; blk < nblk; blk += PU * blk_step) {
+      const bool edge_tile = tc.ty0 + kTH > kHo || tc.tx0 + kTW > kWo;       // tile overhangs the image: interior slots need the bound check
+      auto process_iter = [&](const int itx) {
+        const int blk = blk0 + itx * PU * blk_step;
         uint4 a[PU], r[PU];
 #pragma unroll
         for (int u = 0; u < PU; ++u) {
@@ -719,14 +754,21 @@ __device__ void transform_act16(const TcArgs& args, uint8_t* smem_a, float2* coe
           if (blk + u * blk_step < nblk) {
             *reinterpret_cast<uint4*>(plane + (size_t)q * 16) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
             if (SIDE) {
-              const int hy = (int)(((float)q + 0.5f) * inv_p);
-              const int hx = q - hy * kP;
-              const int iy = hy - kPadT, ix = hx - kPadL;
-              if ((iy >= 0) & (iy < kTH) & (ix >= 0) & (ix < kTW) & (tc.ty0 + iy < kHo) & (tc.tx0 + ix < kWo))
-                *reinterpret_cast<uint4*>(side + (size_t)(side_base + (long long)hy * kWs + hx) * 8) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+              bool own = ((inner_m >> ((itx % RIT) * PU + u)) & 1u) != 0u;
+              if (edge_tile && own) {
+                const int hy = (int)(((float)q + 0.5f) * inv_p);
+                own = (tc.ty0 + hy - kPadT < kHo) & (tc.tx0 + (q - hy * kP) - kPadL < kWo);
+              }
+              if (own) *reinterpret_cast<uint4*>(side + (size_t)(side_base + soff[itx % RIT][u]) * 8) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
             }
           }
         }
+      };
+      if constexpr (SIDE) {
+#pragma unroll
+        for (int itx = 0; itx < RIT; ++itx) { if (itx < nit) process_iter(itx); }
+      } else {
+        for (int itx = 0; itx < nit; ++itx) process_iter(itx);
       }
       if (border) {
         // Out-of-image slots form a frame of `top` / `bot` rows and `left` / `right` columns around the in-image rectangle: only those are
@@ -970,6 +1012,7 @@ __device__ __noinline__ void epilogue_swap(const TcArgs& args, uint32_t tmem_bas
   const size_t plane_slots = (size_t)Ho * Wo;      // 16-byte slots per 8-channel plane
   uint4* const out_base = reinterpret_cast<uint4*>(p.out);
   const int c8 = p.Cout >> 3;
+  const bool csplit = p.out_colsplit != 0;
   double sum_d = 0.0, sq_d = 0.0;
   int cur_n = -1;
   auto flush = [&]() {
@@ -998,7 +1041,7 @@ __device__ __noinline__ void epilogue_swap(const TcArgs& args, uint32_t tmem_bas
       const int tx = m - ty * P;
       const int oy = tc.ty0 + ty, ox = tc.tx0 + tx;
       const bool valid = (ty < TH) & (tx < TW) & (oy < Ho) & (ox < Wo);
-      const int pix = valid ? oy * Wo + ox : -1;
+      const int pix = valid ? oy * Wo + (csplit ? (ox & 1) * ((Wo + 1) >> 1) + (ox >> 1) : ox) : -1;
       const uint32_t vmask = __ballot_sync(0xffffffffu, valid);
       const long long tA = wprof.buf ? clock64() : 0;
       tmem_ld_wait();
@@ -1128,8 +1171,10 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
       else if (t.phase_mode == 2 && t.k16_per_ent == 2 && t.MB == 2) mma_role_phase<2, 2, 2>(t, mc);
       else mma_role_phase<1, 0, 0>(t, mc);
     }
-    else if (t.swap_ab && t.MB == 2) mma_role<2, 2, 1, true>(t, mc);
-    else if (t.swap_ab) mma_role<2, 1, 1, true>(t, mc);
+    else if (t.swap_ab && t.k16_per_ent == 2 && t.MB == 2) mma_role<2, 2, 1, true>(t, mc);
+    else if (t.swap_ab && t.k16_per_ent == 2) mma_role<2, 1, 1, true>(t, mc);
+    else if (t.swap_ab && t.MB == 2) mma_role<1, 2, 1, true>(t, mc);
+    else if (t.swap_ab) mma_role<1, 1, 1, true>(t, mc);
     else if (t.nterms == 3 && t.k16_per_ent == 1 && t.MB == 4) mma_role<1, 4, 3>(t, mc);
     else if (t.nterms == 3 && t.k16_per_ent == 1 && t.MB == 2) mma_role<1, 2, 3>(t, mc);
     else if (t.nterms == 3 && t.k16_per_ent == 1 && t.MB == 1) mma_role<1, 1, 3>(t, mc);
@@ -1271,7 +1316,8 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
               if (valid) {
                 // planar-8 store: 8 channels of a pixel = one slot; a warp's 32 rows are 32 consecutive pixels of an output row
                 // (phase layers: 64), so each plane receives full 128-byte lines
-                const size_t pix = p.phase_mode ? ((size_t)(2 * oy + pa) * Wout + 2 * ox) : ((size_t)oy * Wout + ox);
+                const size_t pix = p.phase_mode ? ((size_t)(2 * oy + pa) * Wout + 2 * ox)
+                                                : ((size_t)oy * Wout + (p.out_colsplit ? (ox & 1) * ((Wout + 1) >> 1) + (ox >> 1) : ox));
                 if (p.out16) {
                   __half* o = (__half*)p.out + plane0 + pix * 8;
 #pragma unroll

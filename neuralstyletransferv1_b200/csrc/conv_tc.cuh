@@ -58,6 +58,7 @@ struct TcPlan {
   // into the operand stage with cp.async.bulk.tensor (one box per 8-channel plane; four parity boxes per plane on stride-2
   // layers), the transform warps apply InstanceNorm / ReLU / residual IN PLACE (shared -> shared), then mirror the borders.
   int tma_mode;
+  int tma_wide;             // tensor maps are 3-D over 8-byte elements (a box row = one contiguous run of P slots) instead of 4-D fp16
   int tma_rows;             // box rows: halo_h (stride 1) or TH + 1 (one stride-2 parity sub-plane)
   int npos_used;            // positions the transform sweeps: halo_h * P (stride 1) or 4 * SUBPOS (stride 2)
   uint32_t a_res_off;       // byte offset of the residual staging planes inside an operand stage (0 = no residual operand)

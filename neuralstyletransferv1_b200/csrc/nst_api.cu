@@ -398,6 +398,11 @@ static bool tc_layout(const ConvParams& p, TcPlan& t, int MB, int bTH, int bTW, 
     t.NPOS = std::max(MBu * 128 + max_off + 2, 4 * t.SUBPOS);
     t.tma_rows = bTH + 1; t.npos_used = 4 * t.SUBPOS;
   }
+  if (tma && p.side_out != nullptr) {
+    // the transform keeps the in-plane offsets of the slots a thread visits in registers: at most 2 iterations x 4 slots per chunk
+    const int nblk = (t.npos_used + 7) / 8, blk_step = t.prod_warps * 32 / (8 * t.planes);
+    if (blk_step < 1 || (nblk + blk_step - 1) / blk_step > 8) return false;
+  }
   if (tma) {
     // TMA destinations (one box per plane) must be 128-byte aligned; the in-place transform touches a plane 128 bytes per
     // quarter-warp, so any plane stride is bank-conflict free.  Box extents are limited to 256 per dimension.
@@ -427,11 +432,19 @@ static bool tc_layout(const ConvParams& p, TcPlan& t, int MB, int bTH, int bTW, 
   if (a_stages < 1) return false;
   if (tma && a_stages < 2) return false;                                 // the loader must be able to run a stage ahead of the transform
   t.a_stages = std::min(a_stages, std::min(TC_MAX_A_STAGES, want + 1));
+  int b_stages = t.b_stages;
+  if (!t.b_resident && !getenv("NST_NO_DEEP_B")) {
+    // leftover shared memory deepens the weight ring (up to 6 stages): a refill has L2 latency + the queueing of the TMA unit behind
+    // the activation boxes, and the MMA issuer showed 10-30 % of its time waiting for weights with three 24 KB stages
+    const int left = avail - t.a_stages * (int)t.a_stage_bytes;
+    b_stages = std::min(6, t.b_stages + std::max(0, left / (int)t.b_stage_bytes));
+  }
+  t.b_stages = b_stages;
   t.MB = MBu;
   t.tiles_x = ceil_div(p.Wo, t.TW);
   t.tiles_y = ceil_div(p.Ho, t.TH);
   t.num_tiles = t.tiles_x * t.tiles_y * p.N;
-  t.smem_bytes = (uint32_t)(t.a_stages * t.a_stage_bytes + b_total + bar_bytes);
+  t.smem_bytes = (uint32_t)(t.a_stages * t.a_stage_bytes + t.b_stages * (int)t.b_stage_bytes + bar_bytes);
   return true;
 }
 
@@ -753,7 +766,7 @@ static bool tma_eligible(const ConvParams& q, const TcPlan& t, int in16) {
   if (getenv("NST_NO_TMA")) return false;
   if (!in16 || t.nterms != 1 || t.pair_mode || t.is_bf16 || t.a_tplanes != 1) return false;
   if (q.map_mode != MAP_IDENTITY || (q.stride != 1 && q.stride != 2)) return false;
-  if (q.stride == 2 && (q.Hs < 2 || q.Ws < 2)) return false;
+  if (q.stride == 2 && (q.Hs < 2 || q.Ws < 2 || q.resid != nullptr)) return false;
   if (q.Cin % 8 != 0) return false;
   return true;
 }
@@ -878,7 +891,8 @@ static int make_plan(nst_handle* h, int N, int H, int W) {
         q.phase_mode = lp.t.phase_mode; q.map_mode = MAP_IDENTITY; q.pad_mode = lp.t.phase_mode == 1 ? PAD_REPLICATE : PAD_ZERO;
         q.Hc = p.Hs; q.Wc = p.Ws; q.Ho = p.Hs; q.Wo = p.Ws;
       }
-      q.resid = s.resid >= 0 ? (const void*)1 : nullptr;                   // plan-time flag (operand stage holds a residual tile too)
+      q.resid = s.resid >= 0 ? (const void*)1 : nullptr;                   // plan-time flags: the layer has a residual operand / a side output
+      q.side_out = s.side >= 0 ? (void*)1 : nullptr;
       lp.t.tma_mode = tma_eligible(q, lp.t, lp.in16) ? 1 : 0;
       lp.t.rr_tiles = getenv("NST_NO_RR") ? 0 : 1;
       lp.t.epi_groups = 1;
@@ -895,7 +909,7 @@ static int make_plan(nst_handle* h, int N, int H, int W) {
         lp.t.rr_tiles = getenv("NST_NO_RR") ? 0 : 1;
         ok = tc_plan_geometry(q, lp.t, fTH, fMB);
       }
-      q.resid = nullptr;
+      q.resid = nullptr; q.side_out = nullptr;
       if (!ok)
         return fail(NST_ERR_INVALID, "layer %s (%d->%d k%d s%d, %dx%d): no tcgen05 tiling fits; only NST_PREC_FP32_DIRECT runs this shape",
                     s.name.c_str(), s.cin, s.cout, s.ks, s.stride, p.Hs, p.Ws);
@@ -912,6 +926,25 @@ static int make_plan(nst_handle* h, int N, int H, int W) {
       lp.coeff_off = stats_off;
       stats_off += round_up((size_t)nb * s.cout * sizeof(float2), 256);
     }
+  }
+  // A stride-2 TMA-fed layer reads its source through four (row, column) parity views.  When the producer stores every row as
+  // [even columns | odd columns] ("column-split"), a view's columns are contiguous in memory and its boxes move whole 16*P-byte runs;
+  // with the natural layout the TMA unit gathers 16-byte pieces 32 bytes apart and became the limiter of these layers (tcprof: the
+  // MMA warp of conv3 waited 60 % of its time for operands).  Only tensors whose single reader is such a layer are split.
+  if (!getenv("NST_NO_COLSPLIT")) {
+    for (int li = 0; li < nl; ++li) {
+      LayerPlan& lp = h->plans[li];
+      const int c = lp.consumer;
+      if (c < 0 || !lp.use_tc || lp.t.phase_mode || h->specs[li].out == BUF_IMAGE) continue;
+      const LayerPlan& cp = h->plans[c];
+      if (!cp.use_tc || !cp.t.tma_mode || h->specs[c].stride != 2 || h->specs[c].resid >= 0 || h->specs[c].side >= 0) continue;
+      lp.p.out_colsplit = 1;
+      h->plans[c].p.in_colsplit = 1;
+    }
+  }
+  for (int li = 0; li < nl; ++li) {
+    LayerPlan& lp = h->plans[li];
+    lp.t.tma_wide = (lp.use_tc && lp.t.tma_mode && !getenv("NST_NO_TMA_WIDE") && (lp.p.stride == 1 || lp.p.in_colsplit) && lp.t.P <= 128) ? 1 : 0;
   }
   size_t off = 0;
   for (int b = 0; b < NBUF; ++b) {
@@ -959,21 +992,34 @@ static EncodeTiledFn encode_tiled_fn() {
   return fn;
 }
 
-// Tensor map over a view of a planar-8 fp16 activation tensor: dims {8 channels, W, H, N*C/8 planes}; box {8, box_w, box_h, 1}.
-// `sx` / `sy` = 2 selects every second column / row starting at `base` (the parity views of the stride-2 layers).
+// Tensor map over a view of a planar-8 fp16 activation tensor.  `wide` (every contiguous view): 3-D {2*W 8-byte elements, H, N*C/8 planes},
+// box {2*box_w, box_h, 1} -- a box row is one contiguous run of box_w slots.  (With the natural 4-D description {8 channels, W, H,
+// planes} the inner box dimension is a single 16-byte slot and the TMA unit moves ~16 B per clock: measured, it was the limiter of
+// the stride-2 layers and close to it on the residual ones.)  Otherwise 4-D fp16 {8, W, H, planes} with `sx` = 2 selecting every second
+// column (parity views of a source stored in natural column order).  `sy` = 2 selects every second row starting at `base`.
 static int encode_act_map(CUtensorMap* m, const void* base, int W, int H, size_t planes, int sx, int sy, size_t row_bytes, size_t plane_bytes,
-                          int box_w, int box_h) {
+                          int box_w, int box_h, bool wide) {
   EncodeTiledFn fn = encode_tiled_fn();
   if (fn == nullptr) return fail(NST_ERR_CUDA, "cuTensorMapEncodeTiled is not available from this driver");
-  const cuuint64_t dims[4] = {8, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)planes};
-  const cuuint64_t strides[3] = {(cuuint64_t)(16 * sx), (cuuint64_t)(row_bytes * sy), (cuuint64_t)plane_bytes};
-  const cuuint32_t box[4] = {8, (cuuint32_t)box_w, (cuuint32_t)box_h, 1};
-  const cuuint32_t estr[4] = {1, 1, 1, 1};
-  const CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 4, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                        CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  CUresult r;
+  if (wide) {
+    const cuuint64_t dims[3] = {(cuuint64_t)(2 * W), (cuuint64_t)H, (cuuint64_t)planes};
+    const cuuint64_t strides[2] = {(cuuint64_t)(row_bytes * sy), (cuuint64_t)plane_bytes};
+    const cuuint32_t box[3] = {(cuuint32_t)(2 * box_w), (cuuint32_t)box_h, 1};
+    const cuuint32_t estr[3] = {1, 1, 1};
+    r = fn(m, CU_TENSOR_MAP_DATA_TYPE_UINT64, 3, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+           CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  } else {
+    const cuuint64_t dims[4] = {8, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)planes};
+    const cuuint64_t strides[3] = {(cuuint64_t)(16 * sx), (cuuint64_t)(row_bytes * sy), (cuuint64_t)plane_bytes};
+    const cuuint32_t box[4] = {8, (cuuint32_t)box_w, (cuuint32_t)box_h, 1};
+    const cuuint32_t estr[4] = {1, 1, 1, 1};
+    r = fn(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 4, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+           CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  }
   if (r != CUDA_SUCCESS)
-    return fail(NST_ERR_CUDA, "cuTensorMapEncodeTiled failed (%d) for view %dx%d planes=%zu strides=%d/%zu/%zu box=%dx%d", (int)r, W, H, planes,
-                16 * sx, row_bytes * sy, plane_bytes, box_w, box_h);
+    return fail(NST_ERR_CUDA, "cuTensorMapEncodeTiled failed (%d) for view %dx%d planes=%zu strides=%d/%zu/%zu box=%dx%d wide=%d", (int)r, W, H, planes,
+                16 * sx, row_bytes * sy, plane_bytes, box_w, box_h, (int)wide);
   return NST_OK;
 }
 
@@ -982,13 +1028,16 @@ static int encode_layer_maps(LayerPlan& lp, const ConvParams& p, const void* src
   const size_t planes = (size_t)nb * (p.Cin >> 3);
   const size_t row_bytes = (size_t)p.Ws * 16, plane_bytes = (size_t)p.Hs * p.Ws * 16;
   int rc;
+  const bool wide = t.tma_wide != 0;
   if (p.stride == 1) {
-    if ((rc = encode_act_map(&lp.tmap[0], src, p.Ws, p.Hs, planes, 1, 1, row_bytes, plane_bytes, t.P, t.tma_rows)) != NST_OK) return rc;
-    if (resid != nullptr && (rc = encode_act_map(&lp.tmap_res, resid, p.Ws, p.Hs, planes, 1, 1, row_bytes, plane_bytes, t.P, t.tma_rows)) != NST_OK) return rc;
+    if ((rc = encode_act_map(&lp.tmap[0], src, p.Ws, p.Hs, planes, 1, 1, row_bytes, plane_bytes, t.P, t.tma_rows, wide)) != NST_OK) return rc;
+    if (resid != nullptr && (rc = encode_act_map(&lp.tmap_res, resid, p.Ws, p.Hs, planes, 1, 1, row_bytes, plane_bytes, t.P, t.tma_rows, wide)) != NST_OK) return rc;
   } else {
     for (int py = 0; py < 2; ++py) for (int px = 0; px < 2; ++px) {
-      const char* base = (const char*)src + ((size_t)py * p.Ws + px) * 16;
-      rc = encode_act_map(&lp.tmap[py * 2 + px], base, (p.Ws - px + 1) / 2, (p.Hs - py + 1) / 2, planes, 2, 2, row_bytes, plane_bytes, t.P, t.tma_rows);
+      // column-split source: the odd columns of a row start (Ws + 1) / 2 slots in and are contiguous
+      const char* base = (const char*)src + ((size_t)py * p.Ws + (p.in_colsplit ? (size_t)px * ((p.Ws + 1) / 2) : (size_t)px)) * 16;
+      rc = encode_act_map(&lp.tmap[py * 2 + px], base, (p.Ws - px + 1) / 2, (p.Hs - py + 1) / 2, planes, p.in_colsplit ? 1 : 2, 2, row_bytes, plane_bytes,
+                          t.P, t.tma_rows, wide);
       if (rc != NST_OK) return rc;
     }
   }

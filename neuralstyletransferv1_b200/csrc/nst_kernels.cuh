@@ -53,6 +53,9 @@ struct ConvParams {
                             // channels [co_off, co_off + co_pass) (co_pass = Cout, co_off = 0 for every other layer)
   int phase_mode;           // sub-pixel form of upsample x2 + conv3: (Ho, Wo) is the LOW-RES tile grid, GEMM column = phase*Cout + co,
                             // phase (a,b) of grid position (i,j) is output pixel (2i+a, 2j+b) of the [N, 2Ho, 2Wo, Cout] tensor
+  int out_colsplit;         // store every output row as [even columns | odd columns]: the single reader is a stride-2 TMA-fed layer whose
+                            // column-parity views are then contiguous in memory (pixel x sits at slot (x & 1) * ((Wo + 1) / 2) + (x >> 1))
+  int in_colsplit;          // the source tensor is stored that way
   int out_fmt;
   void* out;                // OUT_F32_NHWC_STATS: act planar-8 [N,Cout/8,Ho,Wo,8]; OUT_F32_NCHW3: float [N,3,Ho,Wo]; OUT_U8: u8 [N,Ho,Wo,3]
   double* out_part;         // [parts][N][Cout][2] per-CTA partial (sum, sumsq); part = blockIdx.x (tcgen05 kernel) or 0 (direct kernel, atomics)
