@@ -98,13 +98,23 @@ int nst_forward_f32_nchw(nst_handle* h, const float* x, float* y, int N, int H, 
  * narrows it), so y_u8 is bit-identical to the reference's pack of the same fp32 network output.
  * x: [dev] uint8 NHWC [N,H,W,3]; y: [dev] uint8 NHWC [N,Ho,Wo,3] with (Ho,Wo) = nst_output_shape(H,W) -- equal to (H,W) when
  * H,W are multiples of 4 (always for NST).  Otherwise the frame comes back Ho x Wo like the reference module's output and the
- * caller resizes it (pipeline.py:1512-1516, nst_resize_bilinear_u8); mask / blend then require the resize first (NST_ERR_INVALID).
+ * caller resizes it (pipeline.py:1512-1516; nst_forward_u8_nhwc_fit does both); mask / blend then require the resize first (NST_ERR_INVALID).
  * mask: [dev] fp32 [N,H,W] or NULL. */
 int nst_forward_u8_nhwc(nst_handle* h, const uint8_t* x, uint8_t* y, int N, int H, int W,
                         const float in_scale[3], const float in_shift[3],
                         const float out_div[3], const float out_scale[3], const float out_shift[3], int swap_rb,
                         double blend, const float* mask, int composite_mode,
                         void* workspace, size_t workspace_bytes, void* stream);
+
+/* Same fused uint8 path, but the result is always [N,H,W,3]: when H or W is not a multiple of 4 the generator's larger out01 frame is
+ * resized back with the reference's bilinear `F.interpolate(out01, size=(H0, W0), align_corners=False)` BEFORE the mask composite,
+ * blend and pack (pipeline.py:1512-1516 "lock stylized to content size").  This is the call a frame loop makes
+ * (neuralstyletransferv1_b200/frame_pipeline.py); y: [dev] uint8 NHWC [N,H,W,3]. */
+int nst_forward_u8_nhwc_fit(nst_handle* h, const uint8_t* x, uint8_t* y, int N, int H, int W,
+                            const float in_scale[3], const float in_shift[3],
+                            const float out_div[3], const float out_scale[3], const float out_shift[3], int swap_rb,
+                            double blend, const float* mask, int composite_mode,
+                            void* workspace, size_t workspace_bytes, void* stream);
 
 /* ---- compositing --------------------------------------------------------------------------- */
 
@@ -124,6 +134,42 @@ int nst_composite_regions_f32(const float* const* srcs, int K, const float* orig
                               const float* masks, int R, int J,
                               const int* region_idx, const float* region_w,
                               float* out, int H, int W, void* stream);
+
+/* Batched form of the two above (one launch for N frames), replacing the per-frame Python loop around composite_regions /
+ * composite_regions_advanced (pipeline.py:1630-1700; region_blend.py:1049-1108, 1589-1679 including the per-scale bilinear upscale of
+ * :1662-1668).  srcs[k]: [dev] uint8 [N, src_hw[2k], src_hw[2k+1], 3] (src_hw NULL = every source is H x W); a smaller source is
+ * upscaled per pixel like F.interpolate(bilinear, align_corners=False).  masks: [dev] [R,H,W] shared by the batch
+ * (masks_per_frame = 0) or [N,R,H,W]; mask_type 0 = fp32, 1 = fp16, 2 = uint8 (value / 255).  region_idx: -1 = original, -2 = unused
+ * padding entry of a region with fewer than J terms. */
+int nst_composite_regions_batch_u8(const uint8_t* const* srcs, const int* src_hw, int K, const uint8_t* original,
+                                   const void* masks, int mask_type, int masks_per_frame, int R, int J,
+                                   const int* region_idx, const float* region_w,
+                                   uint8_t* out, int N, int H, int W, void* stream);
+
+/* Replaces: region_blend.composite_from_crops + place_crop (region_blend.py:2186-2294, 2080-2109) -- the compositing step of crop-based
+ * region styling (pipeline.py:1293-1400).  Region r covers the padded bounding box bbox[4r..4r+3] = (x1, y1, x2, y2) of the H x W canvas and
+ * blends nterms[r] <= 4 sources: term_src[4r+j] is a [dev] fp32 [3, term_hw[2(4r+j)], term_hw[2(4r+j)+1]] styled crop (0..1), or NULL for
+ * the original frame's crop; a crop whose size differs from the box is resized bilinearly like the reference does.  crop_masks[r]:
+ * [dev] fp32 [mask_hw[2r], mask_hw[2r+1]].  canvas += (sum_j w_j * src_j) * mask; weight += mask; where weight < 0.1 the original fills
+ * the gap (or, without an original, three max-pool dilations 5 / 11 / 21 -- `scratch` = 8*H*W floats [dev] is then required);
+ * out = clamp(canvas / max(weight, 1e-6), 0, 1) as fp32 [3,H,W]; out_u8 (optional) receives its truncating uint8 HWC pack. */
+int nst_composite_from_crops_f32(int R, const int* bbox, const float* const* crop_masks, const int* mask_hw, const int* nterms,
+                                 const float* const* term_src, const int* term_hw, const float* term_w,
+                                 const float* original, float* out, uint8_t* out_u8, float* scratch, int H, int W, void* stream);
+
+/* Replaces: the tail of the per-frame loop on an fp32 out01 frame (pipeline.py:1512-1516 resize to the content size, :2040-2043 mask
+ * composite, :2088-2092 blend, :2094 ToPILImage pack).  src01: [dev] fp32 [N,3,Hi,Wi] in 0..1; out: [dev] uint8 [N,H,W,3]; original
+ * ([dev] uint8 [N,H,W,3]) is needed when mask ([dev] fp32 [N,H,W]) or a blend in [0,1) is given.  Hi x Wi == H x W is the identity resize. */
+int nst_resize_post_pack_u8(const float* src01, int N, int Hi, int Wi, const uint8_t* original, const float* mask, double blend,
+                            int composite_mode, uint8_t* out, int H, int W, void* stream);
+
+/* ---- temporal post-processing --------------------------------------------------------------- */
+
+/* Replaces: `_warp_with_flow` + the flow-guided EMA lerp (pipeline.py:425-439, 1918-1931): warp the previous fused frame along the
+ * optical flow with cv2.remap's bilinear rule (map quantised to 1/32 pixel, replicate border) and blend
+ * out = clip(alpha * curr + (1 - alpha) * warped, 0, 1).  All images [dev] fp32 HWC [H,W,3] in 0..1, flow [dev] fp32 [H,W,2] = (dx, dy);
+ * alpha is clamped to [0,1].  out may alias curr, not prev.  (The flow estimate itself stays in OpenCV) */
+int nst_flow_ema_f32(const float* curr, const float* prev, const float* flow, float* out, int H, int W, double alpha, void* stream);
 
 /* ---- introspection ------------------------------------------------------------------------- */
 

@@ -16,6 +16,7 @@ NST_OK = 0
 ARCH = {"johnson": 0, "nst": 1, "reconet": 2}
 PRECISION = {"f16": 0, "f16x3": 1, "bf16": 2, "fp32_direct": 3}
 COMPOSITE_MODE = {"keep": 0, "replace": 1}
+MASK_TYPE = {"float32": 0, "float16": 1, "uint8": 2}
 
 # symbol -> (restype, argtypes); must list every function include/b200nst.h declares
 _c_float3 = C.POINTER(C.c_float)
@@ -31,6 +32,18 @@ PROTOTYPES = {
     "nst_forward_u8_nhwc": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int,
                                       _c_float3, _c_float3, _c_float3, _c_float3, _c_float3, C.c_int, C.c_double,
                                       C.c_void_p, C.c_int, C.c_void_p, C.c_size_t, C.c_void_p]),
+    "nst_forward_u8_nhwc_fit": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int,
+                                          _c_float3, _c_float3, _c_float3, _c_float3, _c_float3, C.c_int, C.c_double,
+                                          C.c_void_p, C.c_int, C.c_void_p, C.c_size_t, C.c_void_p]),
+    "nst_composite_regions_batch_u8": (C.c_int, [C.POINTER(C.c_void_p), C.POINTER(C.c_int), C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int,
+                                                 C.c_int, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_float), C.c_void_p, C.c_int, C.c_int,
+                                                 C.c_int, C.c_void_p]),
+    "nst_composite_from_crops_f32": (C.c_int, [C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_void_p), C.POINTER(C.c_int), C.POINTER(C.c_int),
+                                               C.POINTER(C.c_void_p), C.POINTER(C.c_int), C.POINTER(C.c_float), C.c_void_p, C.c_void_p,
+                                               C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
+    "nst_resize_post_pack_u8": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_double, C.c_int, C.c_void_p,
+                                          C.c_int, C.c_int, C.c_void_p]),
+    "nst_flow_ema_f32": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_double, C.c_void_p]),
     "nst_composite_regions_u8": (C.c_int, [C.POINTER(C.c_void_p), C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int,
                                            C.POINTER(C.c_int), C.POINTER(C.c_float), C.c_void_p, C.c_int, C.c_int,
                                            C.c_void_p]),

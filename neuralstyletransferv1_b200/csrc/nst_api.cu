@@ -31,6 +31,30 @@ struct CompositeArgs {
 cudaError_t launch_composite(const CompositeArgs& a, bool u8, cudaStream_t stream);
 cudaError_t launch_stats_finalize(const double* part, int parts, int groups, int rr, int N, int C, int tiles_per_img, double inv_count,
                                   const float* gamma, const float* beta, float2* coeff, cudaStream_t stream);
+// postproc.cu
+struct ResizePackArgs {
+  const float* src01; const uint8_t* orig; const float* mask; uint8_t* out;
+  int N, Hi, Wi, H, W; float blend, blend_comp; int composite_mode;
+};
+cudaError_t launch_resize_post_pack(const ResizePackArgs& a, cudaStream_t stream);
+constexpr int CB_MAX_R = 16, CB_MAX_J = 4, CB_MAX_K = 8;
+struct CompositeBatchArgs {
+  const void* srcs[CB_MAX_K]; int src_h[CB_MAX_K], src_w[CB_MAX_K];
+  const uint8_t* original; const void* masks; uint8_t* out;
+  int N, K, R, J, H, W; int mask_type; size_t mask_frame_stride;
+  int idx[CB_MAX_R * CB_MAX_J]; float w[CB_MAX_R * CB_MAX_J];
+};
+cudaError_t launch_composite_batch(const CompositeBatchArgs& a, cudaStream_t stream);
+struct CropTerm { const float* src; int sh, sw; float weight; };
+struct CropRegion { int x1, y1, x2, y2; const float* mask; int mh, mw; int nterms; CropTerm term[CB_MAX_J]; };
+struct CompositeCropsArgs {
+  CropRegion reg[CB_MAX_R]; int R, H, W; const float* original; float* canvas; float* weight; uint8_t* out_u8; int finish;
+};
+cudaError_t launch_composite_crops(const CompositeCropsArgs& a, cudaStream_t stream);
+struct CropsDilateArgs { const float* canvas_in; const float* weight_in; float* canvas_out; float* weight_out; uint8_t* out_u8; int H, W, k, last; };
+cudaError_t launch_crops_dilate(const CropsDilateArgs& a, cudaStream_t stream);
+struct FlowEmaArgs { const float* curr; const float* prev; const float* flow; float* out; int H, W; float alpha, alpha_comp; };
+cudaError_t launch_flow_ema(const FlowEmaArgs& a, cudaStream_t stream);
 }  // namespace nst
 
 using namespace nst;
@@ -214,6 +238,7 @@ struct nst_handle {
   size_t act_bytes_per_frame = 0;
   int act16 = 0;                     // default element type of intermediate activations (layers next to an F16X3 layer differ)
   size_t stats_bytes = 0;            // partial tables + coefficient tables of one micro-batch
+  size_t fit_bytes = 0;              // out01 planes of one micro-batch (uint8 "fit" surface at sizes that are not multiples of 4)
   size_t workspace_bytes = 0;
   unsigned int* err_host = nullptr;
   unsigned int* err_dev = nullptr;
@@ -953,7 +978,9 @@ static int make_plan(nst_handle* h, int N, int H, int W) {
   }
   h->act_bytes_per_frame = off;
   h->stats_bytes = stats_off;
-  h->workspace_bytes = round_up(off * nb, 256) + round_up(stats_off, 256) + 256;
+  // out01 planes of one micro-batch for the resize-back pass of the uint8 "fit" surface (sizes that are not multiples of 4)
+  h->fit_bytes = (h->out_H != H || h->out_W != W) ? round_up((size_t)nb * 3 * h->out_H * h->out_W * sizeof(float), 256) : 0;
+  h->workspace_bytes = round_up(off * nb, 256) + round_up(stats_off, 256) + h->fit_bytes + 256;
   h->plan_N = N; h->plan_H = H; h->plan_W = W; h->plan_nb = nb;
   return NST_OK;
 }
@@ -975,6 +1002,7 @@ struct IoSpec {
   const void* x; void* y;
   float in_scale[3], in_shift[3], out_div[3], out_scale[3], out_shift[3];
   int swap_rb; double blend; const float* mask; int composite_mode;
+  int fit;        // uint8 surface only: the result is H x W; frames whose size is not a multiple of 4 are resized back (pipeline.py:1512-1516)
 };
 
 // cuTensorMapEncodeTiled through the runtime's driver-entry-point lookup (libcuda is not linked)
@@ -1085,7 +1113,9 @@ static int run_forward(nst_handle* h, const IoSpec& io, int N, int H, int W, voi
   char* act = (char*)workspace;
   char* stats = (char*)workspace + round_up(h->act_bytes_per_frame * nb, 256);
   const int Ho = h->out_H, Wo = h->out_W;
-  const size_t in_px = (size_t)H * W * 3, out_px = (size_t)Ho * Wo * 3;
+  const bool fit_resize = io.fit && (Ho != H || Wo != W);
+  float* fit_buf = (float*)(stats + round_up(h->stats_bytes, 256));
+  const size_t in_px = (size_t)H * W * 3, out_px = fit_resize ? in_px : (size_t)Ho * Wo * 3;
   const size_t in_elt = io.in_fmt == IN_U8_NHWC3 ? 1 : 4, out_elt = io.out_fmt == OUT_U8_NHWC3 ? 1 : 4;
   const bool blend_on = io.blend >= 0.0 && io.blend < 1.0;                 // pipeline.py:2089
   std::vector<cudaEvent_t> ev;
@@ -1119,16 +1149,16 @@ static int run_forward(nst_handle* h, const IoSpec& io, int N, int H, int W, voi
       p.side_out = s.side >= 0 ? buf(s.side) : nullptr;
       p.bias = d.bias;
       if (s.out == BUF_IMAGE) {
-        p.out_fmt = io.out_fmt;
-        p.out = (char*)io.y + (size_t)n0 * out_px * out_elt;
+        p.out_fmt = fit_resize ? (int)OUT_F32_01_NCHW3 : io.out_fmt;
+        p.out = fit_resize ? (void*)fit_buf : (void*)((char*)io.y + (size_t)n0 * out_px * out_elt);
         for (int c = 0; c < 3; ++c) { p.out_div[c] = io.out_div[c]; p.out_scale[c] = io.out_scale[c]; p.out_shift[c] = io.out_shift[c]; }
         p.swap_rb = io.swap_rb;
         // Python evaluates `blend * S + (1.0 - blend) * O` with double scalars that torch then narrows to fp32 (pipeline.py:2090)
         p.blend = blend_on ? (float)io.blend : 2.f;
         p.blend_comp = (float)(1.0 - io.blend);
         p.composite_mode = io.composite_mode;
-        p.mask = io.mask ? io.mask + (size_t)n0 * Ho * Wo : nullptr;
-        p.orig = (io.in_fmt == IN_U8_NHWC3 && (io.mask != nullptr || blend_on)) ? (const uint8_t*)io.x + (size_t)n0 * in_px : nullptr;
+        p.mask = (io.mask && !fit_resize) ? io.mask + (size_t)n0 * Ho * Wo : nullptr;
+        p.orig = (io.in_fmt == IN_U8_NHWC3 && !fit_resize && (io.mask != nullptr || blend_on)) ? (const uint8_t*)io.x + (size_t)n0 * in_px : nullptr;
       } else {
         p.out_fmt = OUT_F32_NHWC_STATS;
         p.out = buf(s.out);
@@ -1176,6 +1206,17 @@ static int run_forward(nst_handle* h, const IoSpec& io, int N, int H, int W, voi
       }
       if (layer_ms) CUDA_TRY(cudaEventRecord(ev[li + 1], stream));
     }
+    if (fit_resize) {
+      // "lock stylised to content size" (pipeline.py:1512-1516), then the mask composite / blend / pack the image epilogue skipped
+      ResizePackArgs ra;
+      ra.src01 = fit_buf; ra.out = (uint8_t*)io.y + (size_t)n0 * in_px;
+      ra.orig = (io.mask != nullptr || blend_on) ? (const uint8_t*)io.x + (size_t)n0 * in_px : nullptr;
+      ra.mask = io.mask ? io.mask + (size_t)n0 * H * W : nullptr;
+      ra.N = n; ra.Hi = Ho; ra.Wi = Wo; ra.H = H; ra.W = W;
+      ra.blend = blend_on ? (float)io.blend : 2.f; ra.blend_comp = (float)(1.0 - io.blend); ra.composite_mode = io.composite_mode;
+      CUDA_TRY(launch_resize_post_pack(ra, stream));
+      ++h->launches;
+    }
     if (layer_ms) {
       CUDA_TRY(cudaStreamSynchronize(stream));
       for (size_t li = 0; li < h->specs.size(); ++li) {
@@ -1202,7 +1243,7 @@ extern "C" int nst_forward_f32_nchw(nst_handle* h, const float* x, float* y, int
 
 static int fill_u8_io(nst_handle* h, IoSpec& io, const uint8_t* x, uint8_t* y, int H, int W, const float in_scale[3],
                       const float in_shift[3], const float out_div[3], const float out_scale[3], const float out_shift[3], int swap_rb,
-                      double blend, const float* mask, int composite_mode) {
+                      double blend, const float* mask, int composite_mode, int fit = 0) {
   if (h == nullptr) return fail(NST_ERR_INVALID, "forward_u8: null handle");
   if (!in_scale || !in_shift || !out_div || !out_scale || !out_shift) return fail(NST_ERR_INVALID, "forward_u8: null affine");
   for (int c = 0; c < 3; ++c) if (out_div[c] == 0.f) return fail(NST_ERR_INVALID, "forward_u8: out_div[%d] is zero", c);
@@ -1211,7 +1252,7 @@ static int fill_u8_io(nst_handle* h, IoSpec& io, const uint8_t* x, uint8_t* y, i
   // H or W not a multiple of 4: the stride-2 convs round up, the output is the larger Ho x Wo frame (nst_output_shape) exactly like
   // the reference module's; the caller resizes it back (pipeline.py:1512-1516, frame_pipeline.py).  Blending with the H x W original
   // is only defined after that resize.
-  if ((Ho != H || Wo != W) && (mask != nullptr || (blend >= 0.0 && blend < 1.0)))
+  if (!fit && (Ho != H || Wo != W) && (mask != nullptr || (blend >= 0.0 && blend < 1.0)))
     return fail(NST_ERR_INVALID, "forward_u8: blend / mask need H,W multiples of 4 for this architecture (got %dx%d -> %dx%d); resize first", H, W, Ho, Wo);
   memset(&io, 0, sizeof(io));
   io.in_fmt = IN_U8_NHWC3; io.out_fmt = OUT_U8_NHWC3; io.x = x; io.y = y;
@@ -1219,7 +1260,7 @@ static int fill_u8_io(nst_handle* h, IoSpec& io, const uint8_t* x, uint8_t* y, i
     io.in_scale[c] = in_scale[c]; io.in_shift[c] = in_shift[c];
     io.out_div[c] = out_div[c]; io.out_scale[c] = out_scale[c]; io.out_shift[c] = out_shift[c];
   }
-  io.swap_rb = swap_rb; io.blend = blend; io.mask = mask; io.composite_mode = composite_mode;
+  io.swap_rb = swap_rb; io.blend = blend; io.mask = mask; io.composite_mode = composite_mode; io.fit = fit;
   return NST_OK;
 }
 
@@ -1229,6 +1270,16 @@ extern "C" int nst_forward_u8_nhwc(nst_handle* h, const uint8_t* x, uint8_t* y, 
                                    size_t workspace_bytes, void* stream) {
   IoSpec io;
   int rc = fill_u8_io(h, io, x, y, H, W, in_scale, in_shift, out_div, out_scale, out_shift, swap_rb, blend, mask, composite_mode);
+  if (rc != NST_OK) return rc;
+  return run_forward(h, io, N, H, W, workspace, workspace_bytes, (cudaStream_t)stream, nullptr);
+}
+
+extern "C" int nst_forward_u8_nhwc_fit(nst_handle* h, const uint8_t* x, uint8_t* y, int N, int H, int W, const float in_scale[3],
+                                       const float in_shift[3], const float out_div[3], const float out_scale[3], const float out_shift[3],
+                                       int swap_rb, double blend, const float* mask, int composite_mode, void* workspace,
+                                       size_t workspace_bytes, void* stream) {
+  IoSpec io;
+  int rc = fill_u8_io(h, io, x, y, H, W, in_scale, in_shift, out_div, out_scale, out_shift, swap_rb, blend, mask, composite_mode, 1);
   if (rc != NST_OK) return rc;
   return run_forward(h, io, N, H, W, workspace, workspace_bytes, (cudaStream_t)stream, nullptr);
 }
@@ -1290,6 +1341,107 @@ extern "C" int nst_composite_regions_u8(const uint8_t* const* srcs, int K, const
 extern "C" int nst_composite_regions_f32(const float* const* srcs, int K, const float* original, const float* masks, int R, int J,
                                          const int* region_idx, const float* region_w, float* out, int H, int W, void* stream) {
   return composite_common((const void* const*)srcs, K, original, masks, R, J, region_idx, region_w, out, H, W, stream, false);
+}
+
+extern "C" int nst_composite_regions_batch_u8(const uint8_t* const* srcs, const int* src_hw, int K, const uint8_t* original, const void* masks,
+                                              int mask_type, int masks_per_frame, int R, int J, const int* region_idx, const float* region_w,
+                                              uint8_t* out, int N, int H, int W, void* stream) {
+  if (K < 1 || K > CB_MAX_K || R < 1 || R > CB_MAX_R || J < 1 || J > CB_MAX_J)
+    return fail(NST_ERR_INVALID, "composite_batch: need 1<=K<=%d, 1<=R<=%d, 1<=J<=%d (got K=%d R=%d J=%d)", CB_MAX_K, CB_MAX_R, CB_MAX_J, K, R, J);
+  if (!srcs || !masks || !region_idx || !region_w || !out || N < 1 || H < 1 || W < 1) return fail(NST_ERR_INVALID, "composite_batch: null / empty argument");
+  if (mask_type < 0 || mask_type > 2) return fail(NST_ERR_INVALID, "composite_batch: mask_type must be 0 (fp32), 1 (fp16) or 2 (uint8)");
+  CompositeBatchArgs a;
+  memset(&a, 0, sizeof(a));
+  for (int k = 0; k < K; ++k) {
+    if (!srcs[k]) return fail(NST_ERR_INVALID, "composite_batch: srcs[%d] is null", k);
+    a.srcs[k] = srcs[k];
+    a.src_h[k] = src_hw ? src_hw[2 * k] : H; a.src_w[k] = src_hw ? src_hw[2 * k + 1] : W;
+    if (a.src_h[k] < 1 || a.src_w[k] < 1) return fail(NST_ERR_INVALID, "composite_batch: source %d has extent %dx%d", k, a.src_h[k], a.src_w[k]);
+  }
+  a.original = original; a.masks = masks; a.out = out; a.N = N; a.K = K; a.R = R; a.J = J; a.H = H; a.W = W;
+  a.mask_type = mask_type; a.mask_frame_stride = masks_per_frame ? (size_t)R * H * W : 0;
+  for (int i = 0; i < R * J; ++i) {
+    if (region_idx[i] >= K || region_idx[i] < -2) return fail(NST_ERR_INVALID, "composite_batch: region index %d out of range", region_idx[i]);
+    if (region_idx[i] == -1 && original == nullptr)
+      return fail(NST_ERR_INVALID, "composite_batch: assignment includes original (-1) but no original frame provided");
+    a.idx[i] = region_idx[i]; a.w[i] = region_w[i];
+  }
+  CUDA_TRY(launch_composite_batch(a, (cudaStream_t)stream));
+  return NST_OK;
+}
+
+extern "C" int nst_composite_from_crops_f32(int R, const int* bbox, const float* const* crop_masks, const int* mask_hw, const int* nterms,
+                                            const float* const* term_src, const int* term_hw, const float* term_w, const float* original,
+                                            float* out, uint8_t* out_u8, float* scratch, int H, int W, void* stream) {
+  if (R < 1 || R > CB_MAX_R) return fail(NST_ERR_INVALID, "composite_from_crops: need 1 <= R <= %d (got %d)", CB_MAX_R, R);
+  if (!bbox || !crop_masks || !mask_hw || !nterms || !term_src || !term_hw || !term_w || !out || H < 1 || W < 1)
+    return fail(NST_ERR_INVALID, "composite_from_crops: null / empty argument");
+  CompositeCropsArgs a;
+  memset(&a, 0, sizeof(a));
+  a.R = R; a.H = H; a.W = W; a.original = original;
+  for (int r = 0; r < R; ++r) {
+    CropRegion& g = a.reg[r];
+    g.x1 = bbox[4 * r]; g.y1 = bbox[4 * r + 1]; g.x2 = bbox[4 * r + 2]; g.y2 = bbox[4 * r + 3];
+    if (g.x1 < 0 || g.y1 < 0 || g.x2 > W || g.y2 > H || g.x2 <= g.x1 || g.y2 <= g.y1)
+      return fail(NST_ERR_INVALID, "composite_from_crops: region %d bbox (%d,%d,%d,%d) outside the %dx%d frame", r, g.x1, g.y1, g.x2, g.y2, W, H);
+    g.mask = crop_masks[r]; g.mh = mask_hw[2 * r]; g.mw = mask_hw[2 * r + 1];
+    g.nterms = nterms[r];
+    if (!g.mask || g.mh < 1 || g.mw < 1 || g.nterms < 1 || g.nterms > CB_MAX_J) return fail(NST_ERR_INVALID, "composite_from_crops: region %d is malformed", r);
+    for (int j = 0; j < g.nterms; ++j) {
+      CropTerm& tm = g.term[j];
+      tm.src = term_src[r * CB_MAX_J + j]; tm.sh = term_hw[(r * CB_MAX_J + j) * 2]; tm.sw = term_hw[(r * CB_MAX_J + j) * 2 + 1];
+      tm.weight = term_w[r * CB_MAX_J + j];
+      if (tm.src == nullptr && original == nullptr) return fail(NST_ERR_INVALID, "Region uses original but no original provided");      // region_blend.py:2231
+      if (tm.src != nullptr && (tm.sh < 1 || tm.sw < 1)) return fail(NST_ERR_INVALID, "composite_from_crops: region %d term %d has no extent", r, j);
+    }
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  if (original != nullptr) {
+    a.canvas = out; a.weight = nullptr; a.out_u8 = out_u8; a.finish = 1;
+    CUDA_TRY(launch_composite_crops(a, st));
+    return NST_OK;
+  }
+  // no original: accumulate, then the three max-pool gap-fill passes (region_blend.py:2271-2289); passes after the gaps are closed are
+  // exact no-ops, so the reference's early `break` needs no host round trip.  scratch: 2 x 4 planes of H*W floats.
+  if (scratch == nullptr) return fail(NST_ERR_INVALID, "composite_from_crops: without an original the gap fill needs 8*H*W floats of scratch");
+  const size_t hw = (size_t)H * W;
+  float* bufc[2] = {scratch, scratch + 4 * hw};
+  a.canvas = bufc[0]; a.weight = bufc[0] + 3 * hw; a.out_u8 = nullptr; a.finish = 0;
+  CUDA_TRY(launch_composite_crops(a, st));
+  const int ks[3] = {5, 11, 21};
+  for (int i = 0; i < 3; ++i) {
+    CropsDilateArgs d;
+    d.canvas_in = bufc[i & 1]; d.weight_in = bufc[i & 1] + 3 * hw;
+    d.last = i == 2;
+    d.canvas_out = d.last ? out : bufc[(i + 1) & 1]; d.weight_out = d.last ? nullptr : bufc[(i + 1) & 1] + 3 * hw;
+    d.out_u8 = d.last ? out_u8 : nullptr; d.H = H; d.W = W; d.k = ks[i];
+    CUDA_TRY(launch_crops_dilate(d, st));
+  }
+  return NST_OK;
+}
+
+extern "C" int nst_resize_post_pack_u8(const float* src01, int N, int Hi, int Wi, const uint8_t* original, const float* mask, double blend,
+                                       int composite_mode, uint8_t* out, int H, int W, void* stream) {
+  if (!src01 || !out || N < 1 || Hi < 1 || Wi < 1 || H < 1 || W < 1) return fail(NST_ERR_INVALID, "resize_post_pack: null / empty argument");
+  const bool blend_on = blend >= 0.0 && blend < 1.0;
+  if ((mask != nullptr || blend_on) && original == nullptr) return fail(NST_ERR_INVALID, "resize_post_pack: mask / blend need the original frames");
+  ResizePackArgs ra;
+  ra.src01 = src01; ra.out = out; ra.orig = (mask != nullptr || blend_on) ? original : nullptr; ra.mask = mask;
+  ra.N = N; ra.Hi = Hi; ra.Wi = Wi; ra.H = H; ra.W = W;
+  ra.blend = blend_on ? (float)blend : 2.f; ra.blend_comp = (float)(1.0 - blend); ra.composite_mode = composite_mode;
+  CUDA_TRY(launch_resize_post_pack(ra, (cudaStream_t)stream));
+  return NST_OK;
+}
+
+extern "C" int nst_flow_ema_f32(const float* curr, const float* prev, const float* flow, float* out, int H, int W, double alpha, void* stream) {
+  if (!curr || !prev || !flow || !out || H < 1 || W < 1) return fail(NST_ERR_INVALID, "flow_ema: null / empty argument");
+  if (prev == out) return fail(NST_ERR_INVALID, "flow_ema: out must not alias prev (the warp gathers from it)");
+  FlowEmaArgs a;
+  const double al = std::max(0.0, std::min(1.0, alpha));          // pipeline.py:1927
+  a.curr = curr; a.prev = prev; a.flow = flow; a.out = out; a.H = H; a.W = W;
+  a.alpha = (float)al; a.alpha_comp = (float)(1.0 - al);
+  CUDA_TRY(launch_flow_ema(a, (cudaStream_t)stream));
+  return NST_OK;
 }
 
 // ---------------------------------------------------------------------------------------------

@@ -23,7 +23,8 @@ namespace nst {
 // NST_PREC_F16 mode stores raw conv outputs as fp16: half the HBM traffic, parity cost ~2 dB PSNR --
 // oracle/precision_study.py STORAGE=1), else fp32.
 enum InFmt { IN_F32_NHWC = 0, IN_F32_NCHW3 = 1, IN_U8_NHWC3 = 2 };
-enum OutFmt { OUT_F32_NHWC_STATS = 0, OUT_F32_NCHW3 = 1, OUT_U8_NHWC3 = 2 };
+enum OutFmt { OUT_F32_NHWC_STATS = 0, OUT_F32_NCHW3 = 1, OUT_U8_NHWC3 = 2,
+              OUT_F32_01_NCHW3 = 3 };   // out01 = clamp(post-affine(net output)) as fp32 planes: input of the resize-back pass (postproc.cu)
 enum MapMode { MAP_IDENTITY = 0, MAP_UP2 = 1, MAP_ZERO_INSERT2 = 2, MAP_PREPAD_REFLECT = 3 };
 enum PadMode { PAD_REFLECT = 0, PAD_ZERO = 1, PAD_REPLICATE = 2 };
 
@@ -124,6 +125,18 @@ __device__ __forceinline__ void store_image(const ConvParams& p, int n, int oy, 
     return;
   }
   float s[3] = {v0, v1, v2};
+  if (p.out_fmt == OUT_F32_01_NCHW3) {
+    float* o = (float*)p.out;
+    const size_t plane = (size_t)p.Ho * p.Wo;
+    const size_t base = (size_t)n * 3 * plane + (size_t)oy * p.Wo + ox;
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+      const float y = p.swap_rb ? s[2 - c] : s[c];
+      const float o01 = __fadd_rn(__fmul_rn(__fdiv_rn(y, p.out_div[c]), p.out_scale[c]), p.out_shift[c]);
+      o[base + (size_t)c * plane] = fminf(fmaxf(o01, 0.f), 1.f);
+    }
+    return;
+  }
   uint8_t* o = (uint8_t*)p.out + pix * 3;
   float a = -1.f;
   if (p.mask != nullptr) a = p.mask[pix];

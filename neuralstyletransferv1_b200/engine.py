@@ -145,9 +145,16 @@ class Engine:
         _lib.check(rc, "nst_forward_f32_nchw")
         return y
 
+    def stylize_u8_fit(self, frames: torch.Tensor, preset: str, blend: float = 1.0,
+                       mask: Optional[torch.Tensor] = None, composite_mode: str = "keep",
+                       out: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """``stylize_u8`` whose result always has the input's H x W: sizes that are not multiples of 4 are resized back on the
+        device with the reference's bilinear resize before blending and packing (pipeline.py:1512-1516)."""
+        return self.stylize_u8(frames, preset, blend, mask, composite_mode, out, fit=True)
+
     def stylize_u8(self, frames: torch.Tensor, preset: str, blend: float = 1.0,
                    mask: Optional[torch.Tensor] = None, composite_mode: str = "keep",
-                   out: Optional[torch.Tensor] = None) -> torch.Tensor:
+                   out: Optional[torch.Tensor] = None, fit: bool = False) -> torch.Tensor:
         """uint8 NHWC frames -> stylised uint8 NHWC (whole per-frame path of pipeline.py, fused).
 
         The result is [N, Ho, Wo, 3] with (Ho, Wo) = ``output_shape(H, W)``: the input size when H, W are
@@ -156,13 +163,13 @@ class Engine:
         """
         if frames.dim() == 3:
             return self.stylize_u8(frames[None], preset, blend, None if mask is None else mask[None], composite_mode,
-                                   None if out is None else out[None])[0]
+                                   None if out is None else out[None], fit)[0]
         if frames.dtype != torch.uint8 or frames.dim() != 4 or frames.shape[-1] != 3:
             raise ValueError(f"expected uint8 [N,H,W,3], got {frames.dtype} {tuple(frames.shape)}")
         self._check_dev(frames, "frames")
         frames = frames.contiguous()
         N, H, W, _ = frames.shape
-        Ho, Wo = self.output_shape(H, W)
+        Ho, Wo = (H, W) if fit else self.output_shape(H, W)
         if out is None:
             out = torch.empty(N, Ho, Wo, 3, dtype=torch.uint8, device=frames.device)
         else:
@@ -179,10 +186,10 @@ class Engine:
         s_in, b_in, d_out, s_out, b_out, swap = io_preset_affine(preset)
         ws = self._workspace(N, H, W)
         with torch.cuda.device(self.device):
-            rc = self._lib.nst_forward_u8_nhwc(self._h, frames.data_ptr(), out.data_ptr(), N, H, W,
-                                               _f3(s_in), _f3(b_in), _f3(d_out), _f3(s_out), _f3(b_out), swap, float(blend),
-                                               mptr, _lib.COMPOSITE_MODE[composite_mode],
-                                               ws.data_ptr(), ws.numel(), self._stream())
+            fn = self._lib.nst_forward_u8_nhwc_fit if fit else self._lib.nst_forward_u8_nhwc
+            rc = fn(self._h, frames.data_ptr(), out.data_ptr(), N, H, W,
+                    _f3(s_in), _f3(b_in), _f3(d_out), _f3(s_out), _f3(b_out), swap, float(blend),
+                    mptr, _lib.COMPOSITE_MODE[composite_mode], ws.data_ptr(), ws.numel(), self._stream())
         _lib.check(rc, "nst_forward_u8_nhwc")
         return out
 
@@ -266,4 +273,176 @@ def composite_regions(styled: Sequence[torch.Tensor], masks: torch.Tensor,
                 masks.data_ptr(), R, J, (C.c_int * (R * J))(*flat_i), (C.c_float * (R * J))(*flat_w),
                 out.data_ptr(), H, W, torch.cuda.current_stream(dev).cuda_stream)
     _lib.check(rc, "nst_composite_regions")
+    return out
+
+
+def composite_regions_batch(styled: Sequence[torch.Tensor], masks: torch.Tensor,
+                            model_indices: Sequence[Sequence[int]], model_weights: Optional[Sequence[Sequence[float]]] = None,
+                            original: Optional[torch.Tensor] = None, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """``composite_regions`` / ``composite_regions_advanced`` over a BATCH of frames in one kernel launch.
+
+    styled: K uint8 tensors [N, Hk, Wk, 3]; a source smaller than the frame (a region styled at scale < 1,
+    region_blend.py:1662-1668) is upscaled bilinearly per pixel.  masks: [R,H,W] (shared by the batch) or [N,R,H,W];
+    float32, float16 or uint8 (value / 255).  original: uint8 [N,H,W,3] (index -1).  Returns uint8 [N,H,W,3].
+    """
+    lib = _lib.load()
+    K = len(styled)
+    if K < 1 or not styled[0].is_cuda:
+        raise RuntimeError("composite_regions_batch needs CUDA tensors; there is no CPU path")
+    dev = styled[0].device
+    per_frame = masks.dim() == 4
+    R = masks.shape[1] if per_frame else masks.shape[0]
+    H, W = masks.shape[-2], masks.shape[-1]
+    N = styled[0].shape[0]
+    if len(model_indices) != R or (model_weights is not None and len(model_weights) != R):
+        raise ValueError(f"model_indices / model_weights must have one entry per region ({R})")
+    if str(masks.dtype).replace("torch.", "") not in _lib.MASK_TYPE:
+        raise ValueError(f"masks must be float32, float16 or uint8, got {masks.dtype}")
+    if masks.device != dev or (per_frame and masks.shape[0] != N):
+        raise ValueError(f"masks must be [R,H,W] or [N,R,H,W] on {dev}")
+    for t in styled:
+        if t.dtype != torch.uint8 or t.dim() != 4 or t.shape[0] != N or t.shape[-1] != 3 or t.device != dev:
+            raise ValueError(f"every styled batch must be uint8 [N={N},h,w,3] on {dev}; got {t.dtype} {tuple(t.shape)}")
+    if original is not None and (tuple(original.shape) != (N, H, W, 3) or original.dtype != torch.uint8 or original.device != dev):
+        raise ValueError(f"original must be uint8 {(N, H, W, 3)} on {dev}")
+    idx = [list(ix) if isinstance(ix, (list, tuple)) else [int(ix)] for ix in model_indices]
+    J = max(len(ix) for ix in idx)
+    wts = [list(w) for w in model_weights] if model_weights is not None else [[1.0] * len(ix) for ix in idx]
+    flat_i, flat_w = [], []
+    for ix, w in zip(idx, wts):
+        flat_i += ix + [-2] * (J - len(ix))
+        flat_w += list(w) + [0.0] * (J - len(w))
+    srcs = [t.contiguous() for t in styled]
+    masks = masks.contiguous()
+    orig = original.contiguous() if original is not None else None
+    if out is None:
+        out = torch.empty(N, H, W, 3, dtype=torch.uint8, device=dev)
+    elif tuple(out.shape) != (N, H, W, 3) or out.dtype != torch.uint8 or not out.is_contiguous() or out.device != dev:
+        raise ValueError(f"out must be a contiguous uint8 tensor {(N, H, W, 3)} on {dev}")
+    c_srcs = (C.c_void_p * K)(*[t.data_ptr() for t in srcs])
+    hw = []
+    for t in srcs:
+        hw += [t.shape[1], t.shape[2]]
+    with torch.cuda.device(dev):
+        rc = lib.nst_composite_regions_batch_u8(C.cast(c_srcs, C.POINTER(C.c_void_p)), (C.c_int * (2 * K))(*hw), K,
+                                                orig.data_ptr() if orig is not None else None, masks.data_ptr(),
+                                                _lib.MASK_TYPE[str(masks.dtype).replace("torch.", "")], 1 if per_frame else 0, R, J,
+                                                (C.c_int * (R * J))(*flat_i), (C.c_float * (R * J))(*flat_w),
+                                                out.data_ptr(), N, H, W, torch.cuda.current_stream(dev).cuda_stream)
+    _lib.check(rc, "nst_composite_regions_batch_u8")
+    return out
+
+
+def composite_from_crops(styled_crops, crops, original: Optional[torch.Tensor], H: int, W: int,
+                         return_u8: bool = False):
+    """region_blend.composite_from_crops (region_blend.py:2186-2294) on the device.
+
+    styled_crops: ``{model_idx: {region_idx: fp32 [3,h,w] CUDA tensor}}`` exactly like the reference's nested dict.
+    crops: a sequence of objects / dicts with ``region_idx``, ``padded_bbox`` (x1, y1, x2, y2), ``crop_mask``
+    (fp32 [1,1,h,w] or [h,w]), ``model_indices`` and ``model_weights`` (the reference's ``RegionCrop`` with its
+    ``config`` flattened is accepted as is).  original: fp32 [3,H,W] CUDA tensor or None.  Returns the composited frame
+    fp32 [3,H,W] (and its uint8 [H,W,3] pack when ``return_u8``).
+    """
+    lib = _lib.load()
+    MAXJ = 4
+    R = len(crops)
+    dev = None
+    bbox, mask_hw, nterms, term_hw, term_w = [], [], [], [0] * (R * MAXJ * 2), [0.0] * (R * MAXJ)
+    mask_ptrs, term_ptrs, keep = [], [0] * (R * MAXJ), []
+
+    def field(c, name):
+        if isinstance(c, dict):
+            return c[name]
+        if hasattr(c, name):
+            return getattr(c, name)
+        return getattr(c.config, name)          # RegionCrop.config.model_indices / model_weights
+
+    for r, c in enumerate(crops):
+        x1, y1, x2, y2 = [int(v) for v in field(c, "padded_bbox")]
+        bbox += [x1, y1, x2, y2]
+        m = field(c, "crop_mask")
+        m = m.reshape(m.shape[-2], m.shape[-1]).to(torch.float32).contiguous()
+        if not m.is_cuda:
+            raise RuntimeError("composite_from_crops needs CUDA tensors; there is no CPU path")
+        dev = m.device
+        keep.append(m)
+        mask_ptrs.append(m.data_ptr())
+        mask_hw += [m.shape[0], m.shape[1]]
+        idxs, wts = list(field(c, "model_indices")), list(field(c, "model_weights"))
+        if not 1 <= len(idxs) <= MAXJ:
+            raise ValueError(f"region {r}: 1..{MAXJ} blended models per region are supported")
+        nterms.append(len(idxs))
+        for j, (mi, wt) in enumerate(zip(idxs, wts)):
+            term_w[r * MAXJ + j] = float(wt)
+            if mi == -1:
+                if original is None:
+                    raise ValueError("Region uses original but no original provided")           # region_blend.py:2231
+                continue
+            if mi not in styled_crops:
+                raise ValueError(f"Model {mi} not in styled_crops")                             # region_blend.py:2236
+            ridx = int(field(c, "region_idx"))
+            if ridx not in styled_crops[mi]:
+                raise ValueError(f"Region {ridx} not styled by model {mi}")                     # region_blend.py:2238
+            t = styled_crops[mi][ridx].to(torch.float32).contiguous()
+            keep.append(t)
+            term_ptrs[r * MAXJ + j] = t.data_ptr()
+            term_hw[(r * MAXJ + j) * 2], term_hw[(r * MAXJ + j) * 2 + 1] = t.shape[-2], t.shape[-1]
+    orig = None
+    if original is not None:
+        orig = original.reshape(3, H, W).to(torch.float32).contiguous()
+        dev = orig.device
+    out = torch.empty(3, H, W, dtype=torch.float32, device=dev)
+    out_u8 = torch.empty(H, W, 3, dtype=torch.uint8, device=dev) if return_u8 else None
+    scratch = None if orig is not None else torch.empty(8 * H * W, dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev):
+        rc = lib.nst_composite_from_crops_f32(
+            R, (C.c_int * (4 * R))(*bbox), C.cast((C.c_void_p * R)(*mask_ptrs), C.POINTER(C.c_void_p)), (C.c_int * (2 * R))(*mask_hw),
+            (C.c_int * R)(*nterms), C.cast((C.c_void_p * (R * MAXJ))(*[p or None for p in term_ptrs]), C.POINTER(C.c_void_p)),
+            (C.c_int * (R * MAXJ * 2))(*term_hw), (C.c_float * (R * MAXJ))(*term_w),
+            orig.data_ptr() if orig is not None else None, out.data_ptr(), out_u8.data_ptr() if out_u8 is not None else None,
+            scratch.data_ptr() if scratch is not None else None, H, W, torch.cuda.current_stream(dev).cuda_stream)
+    _lib.check(rc, "nst_composite_from_crops_f32")
+    return (out, out_u8) if return_u8 else out
+
+
+def flow_ema(curr01: torch.Tensor, prev01: torch.Tensor, flow: torch.Tensor, alpha: float,
+             out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """Flow-guided EMA of pipeline.py:1918-1931: ``clip(a * curr + (1 - a) * remap(prev, grid + flow), 0, 1)``.
+
+    curr01 / prev01: fp32 [H,W,3] CUDA tensors in 0..1 (the reference's numpy layout); flow: fp32 [H,W,2] = (dx, dy).
+    """
+    lib = _lib.load()
+    if not curr01.is_cuda:
+        raise RuntimeError("flow_ema needs CUDA tensors; there is no CPU path")
+    H, W, _ = curr01.shape
+    for t, shp, name in ((curr01, (H, W, 3), "curr01"), (prev01, (H, W, 3), "prev01"), (flow, (H, W, 2), "flow")):
+        if tuple(t.shape) != shp or t.dtype != torch.float32 or t.device != curr01.device:
+            raise ValueError(f"{name} must be float32 {shp} on {curr01.device}")
+    curr01, prev01, flow = curr01.contiguous(), prev01.contiguous(), flow.contiguous()
+    if out is None:
+        out = torch.empty_like(curr01)
+    with torch.cuda.device(curr01.device):
+        rc = lib.nst_flow_ema_f32(curr01.data_ptr(), prev01.data_ptr(), flow.data_ptr(), out.data_ptr(), H, W, float(alpha),
+                                  torch.cuda.current_stream(curr01.device).cuda_stream)
+    _lib.check(rc, "nst_flow_ema_f32")
+    return out
+
+
+def resize_post_pack(out01: torch.Tensor, H: int, W: int, original: Optional[torch.Tensor] = None, mask: Optional[torch.Tensor] = None,
+                     blend: float = 1.0, composite_mode: str = "keep") -> torch.Tensor:
+    """fp32 out01 frames [N,3,h,w] -> uint8 [N,H,W,3]: bilinear resize to the content size (pipeline.py:1512-1516), mask composite,
+    blend, truncating pack (pipeline.py:2040-2094).  original: uint8 [N,H,W,3]; mask: fp32 [N,H,W]."""
+    lib = _lib.load()
+    if not out01.is_cuda:
+        raise RuntimeError("resize_post_pack needs CUDA tensors; there is no CPU path")
+    out01 = out01.to(torch.float32).contiguous()
+    N, _, hi, wi = out01.shape
+    out = torch.empty(N, H, W, 3, dtype=torch.uint8, device=out01.device)
+    orig = original.contiguous() if original is not None else None
+    m = mask.to(torch.float32).contiguous() if mask is not None else None
+    with torch.cuda.device(out01.device):
+        rc = lib.nst_resize_post_pack_u8(out01.data_ptr(), N, hi, wi, orig.data_ptr() if orig is not None else None,
+                                         m.data_ptr() if m is not None else None, float(blend), _lib.COMPOSITE_MODE[composite_mode],
+                                         out.data_ptr(), H, W, torch.cuda.current_stream(out01.device).cuda_stream)
+    _lib.check(rc, "nst_resize_post_pack_u8")
     return out

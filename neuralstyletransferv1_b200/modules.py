@@ -149,10 +149,11 @@ class _B200Generator(nn.Module):
 
     def stylize_u8(self, frames_u8_nhwc: torch.Tensor, io_preset: str, blend: float = 1.0,
                    mask: Optional[torch.Tensor] = None, composite_mode: str = "keep",
-                   out: Optional[torch.Tensor] = None) -> torch.Tensor:
-        """Fused uint8 path (mirrors lib.ReCoNetModel.run, lib.py:27-51, for every family)."""
+                   out: Optional[torch.Tensor] = None, fit: bool = False) -> torch.Tensor:
+        """Fused uint8 path (mirrors lib.ReCoNetModel.run, lib.py:27-51, for every family).  ``fit=True`` returns the input's
+        H x W even when it is not a multiple of 4 (the reference's resize-back of pipeline.py:1512-1516)."""
         eng = self._ensure_engine(frames_u8_nhwc.device)
-        return eng.stylize_u8(frames_u8_nhwc, io_preset, blend, mask, composite_mode, out)
+        return eng.stylize_u8(frames_u8_nhwc, io_preset, blend, mask, composite_mode, out, fit)
 
 
 class TransformerNet(_B200Generator):

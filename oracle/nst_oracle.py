@@ -264,3 +264,104 @@ def u8_metrics(a_u8: Tensor, b_u8: Tensor):
     mse = float((d.to(torch.float64) ** 2).mean())
     psnr = float("inf") if mse == 0 else 10.0 * torch.log10(torch.tensor(255.0 ** 2 / mse)).item()
     return mx, psnr
+
+
+# --------------------------------------------------------------------------- #
+# round 2: resize-back, multi-scale / batched composite, crop composite, flow EMA
+# (test infrastructure: pinned against the reference's own functions by tests/golden/make_golden.py)
+# --------------------------------------------------------------------------- #
+def stylize_u8_fit(arch: str, sd: SD, frames_u8_nhwc: Tensor, preset: str, blend: float = 1.0,
+                   mask: Optional[Tensor] = None, composite_mode: str = "keep") -> Tensor:
+    """Per-frame path INCLUDING pipeline.py:1512-1516: when the generator returns a larger frame (H or W not a
+    multiple of 4) out01 is resized back with ``F.interpolate(bilinear, align_corners=False)`` before the mask
+    composite, the blend and the pack."""
+    x01 = frames_u8_nhwc.permute(0, 3, 1, 2).to(torch.float32) / 255.0
+    out01 = io_post(forward(arch, sd, io_pre(x01, preset)), preset)
+    if out01.shape[-2:] != x01.shape[-2:]:
+        out01 = F.interpolate(out01, size=tuple(x01.shape[-2:]), mode="bilinear", align_corners=False)
+    return post_u8(out01, x01, blend, mask, composite_mode)
+
+
+def composite_regions_multiscale(styled_by_scale, masks: Sequence[Tensor], configs, original: Optional[Tensor],
+                                 H: int, W: int) -> Tensor:
+    """region_blend.composite_regions_advanced (region_blend.py:1589-1679) with its per-scale sources:
+    ``styled_by_scale`` = {scale: [frame per model, fp32 [3,h,w]]}, ``configs`` = [(model_indices, model_weights, scale)]."""
+    C = 3
+    if original is not None:
+        original = original.reshape(1, C, *original.shape[-2:])
+        if original.shape[-2:] != (H, W):
+            original = F.interpolate(original, size=(H, W), mode="bilinear", align_corners=False)
+    result = torch.zeros(1, C, H, W)
+    wsum = torch.zeros(1, 1, H, W)
+    for m, (idxs, ws, scale) in zip(masks, configs):
+        m = m.reshape(1, 1, *m.shape[-2:])
+        if m.shape[-2:] != (H, W):
+            m = F.interpolate(m, size=(H, W), mode="bilinear", align_corners=False)
+        if scale not in styled_by_scale:
+            scale = min(styled_by_scale.keys(), key=lambda s: abs(s - scale))
+        outs = styled_by_scale[scale]
+        rb = torch.zeros(1, C, H, W)
+        for i, wt in zip(idxs, ws):
+            if i == -1:
+                src = original
+            else:
+                src = outs[i].reshape(1, C, *outs[i].shape[-2:])
+                if src.shape[-2:] != (H, W):
+                    src = F.interpolate(src, size=(H, W), mode="bilinear", align_corners=False)
+            rb += wt * src
+        result += rb * m.expand(1, C, H, W)
+        wsum += m
+    result = result / wsum.expand(1, C, H, W).clamp(min=1e-6)
+    return result.squeeze(0).clamp(0, 1)
+
+
+def composite_from_crops(styled_crops, crops, original: Optional[Tensor], H: int, W: int) -> Tensor:
+    """region_blend.composite_from_crops + place_crop (region_blend.py:2186-2294, 2080-2109), static blend weights.
+    ``crops``: dicts with region_idx, padded_bbox, crop_mask [1,1,h,w], model_indices, model_weights."""
+    C = 3
+    canvas = torch.zeros(C, H, W)
+    wsum = torch.zeros(1, H, W)
+    for c in crops:
+        x1, y1, x2, y2 = c["padded_bbox"]
+        ch, cw = y2 - y1, x2 - x1
+        rb = torch.zeros(C, ch, cw)
+        for mi, wt in zip(c["model_indices"], c["model_weights"]):
+            src = original[:, y1:y2, x1:x2].clone() if mi == -1 else styled_crops[mi][c["region_idx"]]
+            if src.shape[1] != ch or src.shape[2] != cw:
+                src = F.interpolate(src.unsqueeze(0), size=(ch, cw), mode="bilinear", align_corners=False).squeeze(0)
+            rb += wt * src
+        m = c["crop_mask"]
+        if m.shape[2] != ch or m.shape[3] != cw:
+            m = F.interpolate(m, size=(ch, cw), mode="bilinear", align_corners=False)
+        canvas[:, y1:y2, x1:x2] += rb * m.squeeze(0).expand(C, -1, -1)
+        wsum[:, y1:y2, x1:x2] += m.squeeze(0)
+    gap = (wsum < 0.1).float()
+    if gap.sum() > 0:
+        gap3 = gap.expand(C, -1, -1)
+        if original is not None:
+            canvas = canvas + original * gap3
+            wsum = wsum + gap
+        else:
+            for k in (5, 11, 21):
+                cd = F.max_pool2d(canvas.unsqueeze(0), kernel_size=k, stride=1, padding=k // 2).squeeze(0)
+                wd = F.max_pool2d(wsum.unsqueeze(0), kernel_size=k, stride=1, padding=k // 2).squeeze(0)
+                canvas = canvas * (1 - gap3) + cd * gap3
+                wsum = wsum * (1 - gap) + wd * gap
+                gap = (wsum < 0.1).float()
+                gap3 = gap.expand(C, -1, -1)
+                if gap.sum() == 0:
+                    break
+    return (canvas / wsum.expand(C, -1, -1).clamp(min=1e-6)).clamp(0, 1)
+
+
+def flow_ema(curr01_hwc, prev01_hwc, flow_hw2, alpha: float):
+    """pipeline.py:425-439 `_warp_with_flow` (cv2.remap, the reference's own OpenCV call) + :1927-1929 EMA lerp; numpy fp32 HWC."""
+    import cv2
+    import numpy as np
+    H, W = flow_hw2.shape[:2]
+    gx, gy = np.meshgrid(np.arange(W, dtype=np.float32), np.arange(H, dtype=np.float32))
+    map_x = (gx + flow_hw2[..., 0]).astype(np.float32)
+    map_y = (gy + flow_hw2[..., 1]).astype(np.float32)
+    warped = cv2.remap(prev01_hwc, map_x, map_y, interpolation=cv2.INTER_LINEAR, borderMode=cv2.BORDER_REPLICATE)
+    a = float(max(0.0, min(1.0, alpha)))
+    return (a * curr01_hwc + (1.0 - a) * warped).clip(0.0, 1.0).astype("float32")

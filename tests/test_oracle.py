@@ -79,3 +79,89 @@ def test_reconet_run_u8_equals_stylize_tanh():
     b = O.stylize_u8("reconet", sd, u8, "tanh")
     mx, _ = O.u8_metrics(a, b)
     assert mx <= 1       # (y+1)/2*255 vs ((y+1)*0.5).clamp*255: same value up to 1 ulp at a truncation edge
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# round 2: the post-network restatements against fixtures produced by the reference's OWN functions (make_golden.py)
+# ---------------------------------------------------------------------------------------------------------------------
+def _crops_from_fixture(g, only=None):
+    crops, styled = [], {}
+    for r in range(int(g["n_regions"])):
+        if only is not None and r not in only:
+            continue
+        idx = [int(i) for i in g[f"idx{r}"]]
+        crops.append({"region_idx": r, "padded_bbox": tuple(int(v) for v in g[f"bbox{r}"]), "crop_mask": torch.from_numpy(g[f"mask{r}"]),
+                      "model_indices": idx, "model_weights": [float(w) for w in g[f"wts{r}"]]})
+        for mi in idx:
+            if mi >= 0:
+                styled.setdefault(mi, {})[r] = torch.from_numpy(g[f"styled{mi}_{r}"])
+    return crops, styled
+
+
+def test_composite_advanced_multiscale_matches_reference():
+    g = np.load(os.path.join(GOLDEN, "composite_advanced_60x84.npz"))
+    full, half = [torch.from_numpy(a) for a in g["full"]], [torch.from_numpy(a) for a in g["half"]]
+    masks = [torch.from_numpy(m)[None, None] for m in g["masks"]]
+    configs = [([int(i) for i in ix if i > -2], [float(w) for i, w in zip(ix, ws) if i > -2], float(sc))
+               for ix, ws, sc in zip(g["idx"], g["wts"], g["scales"])]
+    out = O.composite_regions_multiscale({1.0: full, 0.5: half}, masks, configs, torch.from_numpy(g["original"]), 60, 84)
+    assert torch.equal(out, torch.from_numpy(g["out"]))
+
+
+def test_composite_from_crops_matches_reference():
+    g = np.load(os.path.join(GOLDEN, "composite_crops_180x240.npz"))
+    crops, styled = _crops_from_fixture(g)
+    out = O.composite_from_crops(styled, crops, torch.from_numpy(g["original"]), 180, 240)
+    assert torch.equal(out, torch.from_numpy(g["out_with_original"]))
+    crops, styled = _crops_from_fixture(g, only=set(int(r) for r in g["no_orig_regions"]))
+    out = O.composite_from_crops(styled, crops, None, 180, 240)
+    assert torch.equal(out, torch.from_numpy(g["out_without_original"]))
+
+
+def test_flow_ema_matches_reference():
+    g = np.load(os.path.join(GOLDEN, "flow_ema_54x70.npz"))
+    fused = O.flow_ema(g["curr"], g["prev"], g["flow"], float(g["alpha"]))
+    assert np.array_equal(fused, g["fused"])
+
+
+def test_fit_path_matches_pipeline_arithmetic():
+    """Odd-sized frame: net -> /255 -> clamp -> bilinear resize back -> mask composite -> blend -> ToPILImage, generated with the
+    pipeline's literal numpy / torch arithmetic around the real TransformerNet (make_golden.py (4))."""
+    g = np.load(os.path.join(GOLDEN, "fit_johnson_50x70.npz"))
+    sd = synth.make_state_dict("johnson", int(g["weight_seed"]))
+    frames = torch.from_numpy(g["frames"])
+    out = O.stylize_u8_fit("johnson", sd, frames, "raw_255", blend=float(g["blend"]), mask=torch.from_numpy(g["alpha"]))
+    assert torch.equal(out[0], torch.from_numpy(g["out_u8"]))
+    plain = O.stylize_u8_fit("johnson", sd, frames, "raw_255")
+    assert torch.equal(plain[0], torch.from_numpy(g["out_u8_plain"]))
+
+
+def test_bilinear_formula_used_by_the_kernels_is_torchs():
+    """csrc/postproc.cu evaluates F.interpolate(bilinear, align_corners=False) as: source index fma(scale, dst + 0.5, -0.5), value
+    fma(wy0, fma(wx0, a, wx1*b), wy1 * fma(wx0, c, wx1*d)).  That is bit-for-bit what ATen's CPU kernel computes (sizes below ~100
+    outputs take a scalar path that differs by 1 ulp)."""
+    f32 = np.float32
+
+    def fma(a, b, c):
+        return (a.astype(np.float64) * b.astype(np.float64) + c.astype(np.float64)).astype(np.float32)
+
+    def coords(i_sz, o_sz):
+        scale = f32(i_sz) / f32(o_sz)
+        d = np.arange(o_sz, dtype=np.float32)
+        real = np.maximum(fma(np.full_like(d, scale), d + f32(0.5), np.full_like(d, -0.5)), f32(0))
+        i0 = np.minimum(np.floor(real).astype(np.int64), i_sz - 1)
+        lam = np.clip(real - i0.astype(np.float32), f32(0), f32(1)).astype(np.float32)
+        return i0, i0 + (i0 < i_sz - 1), (f32(1) - lam).astype(np.float32), lam
+
+    for hi, wi, h, w in ((272, 484, 271, 481), (135, 240, 270, 480), (252, 272, 250, 270)):
+        x = torch.rand(1, 3, hi, wi, generator=torch.Generator().manual_seed(hi))
+        ref = torch.nn.functional.interpolate(x, size=(h, w), mode="bilinear", align_corners=False).numpy()
+        xn = x.numpy()
+        y0, y1, wy0, wy1 = coords(hi, h)
+        x0, x1, wx0, wx1 = coords(wi, w)
+        a, b, c, d = xn[:, :, y0][..., x0], xn[:, :, y0][..., x1], xn[:, :, y1][..., x0], xn[:, :, y1][..., x1]
+        bx = lambda v: np.broadcast_to(v[None, None, None, :], a.shape)
+        by = lambda v: np.broadcast_to(v[None, None, :, None], a.shape)
+        top, bot = fma(bx(wx0), a, bx(wx1) * b), fma(bx(wx0), c, bx(wx1) * d)
+        mine = fma(by(wy0), top, by(wy1) * bot)
+        assert np.array_equal(mine, ref), (hi, wi, h, w)
