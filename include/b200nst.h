@@ -163,6 +163,16 @@ int nst_composite_from_crops_f32(int R, const int* bbox, const float* const* cro
 int nst_resize_post_pack_u8(const float* src01, int N, int Hi, int Wi, const uint8_t* original, const float* mask, double blend,
                             int composite_mode, uint8_t* out, int H, int W, void* stream);
 
+/* ---- region masks --------------------------------------------------------------------------- */
+
+/* Replaces: region_blend.voronoi_masks + feather_mask / gaussian_blur_mask (region_blend.py:174-236, 69-102) for given seed points:
+ * mask_i = GaussianBlur_reflect(argmin_j dist(pixel, point_j) == i), sigma = feather / 3.  points_xy: [host] R (x, y) pairs (the host
+ * draws them exactly like `_generate_balanced_points`, neuralstyletransferv1_b200/region_masks.py); region_weights: [host] R relative
+ * region sizes or NULL.  masks: [dev] fp32 [R,H,W]; scratch: [dev] H*W bytes + R*H*W floats.  The reference convolves with the 2-D
+ * outer-product kernel, this is the separable form: equal to ~1e-6. */
+int nst_voronoi_masks_f32(const float* points_xy, const float* region_weights, int R, int feather, float* masks, float* scratch,
+                          int H, int W, void* stream);
+
 /* ---- temporal post-processing --------------------------------------------------------------- */
 
 /* Replaces: `_warp_with_flow` + the flow-guided EMA lerp (pipeline.py:425-439, 1918-1931): warp the previous fused frame along the

@@ -43,6 +43,8 @@ PROTOTYPES = {
                                                C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
     "nst_resize_post_pack_u8": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_double, C.c_int, C.c_void_p,
                                           C.c_int, C.c_int, C.c_void_p]),
+    "nst_voronoi_masks_f32": (C.c_int, [C.POINTER(C.c_float), C.POINTER(C.c_float), C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int,
+                                        C.c_void_p]),
     "nst_flow_ema_f32": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_double, C.c_void_p]),
     "nst_composite_regions_u8": (C.c_int, [C.POINTER(C.c_void_p), C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int,
                                            C.POINTER(C.c_int), C.POINTER(C.c_float), C.c_void_p, C.c_int, C.c_int,

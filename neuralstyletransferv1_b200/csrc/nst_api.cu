@@ -55,6 +55,11 @@ struct CropsDilateArgs { const float* canvas_in; const float* weight_in; float* 
 cudaError_t launch_crops_dilate(const CropsDilateArgs& a, cudaStream_t stream);
 struct FlowEmaArgs { const float* curr; const float* prev; const float* flow; float* out; int H, W; float alpha, alpha_comp; };
 cudaError_t launch_flow_ema(const FlowEmaArgs& a, cudaStream_t stream);
+constexpr int VOR_MAX_R = 16, BLUR_MAX_K = 255;
+struct VoronoiArgs { float px[VOR_MAX_R], py[VOR_MAX_R], inv_w[VOR_MAX_R]; int R, H, W, weighted; uint8_t* label; };
+cudaError_t launch_voronoi_label(const VoronoiArgs& a, cudaStream_t stream);
+struct BlurArgs { const uint8_t* label; const float* src; float* dst; int R, H, W, k, vertical; float w[BLUR_MAX_K]; };
+cudaError_t launch_blur_pass(const BlurArgs& a, cudaStream_t stream);
 }  // namespace nst
 
 using namespace nst;
@@ -1417,6 +1422,47 @@ extern "C" int nst_composite_from_crops_f32(int R, const int* bbox, const float*
     d.out_u8 = d.last ? out_u8 : nullptr; d.H = H; d.W = W; d.k = ks[i];
     CUDA_TRY(launch_crops_dilate(d, st));
   }
+  return NST_OK;
+}
+
+extern "C" int nst_voronoi_masks_f32(const float* points_xy, const float* region_weights, int R, int feather, float* masks, float* scratch,
+                                     int H, int W, void* stream) {
+  if (!points_xy || !masks || !scratch || R < 1 || R > VOR_MAX_R || H < 2 || W < 2) return fail(NST_ERR_INVALID, "voronoi_masks: bad argument (1 <= R <= %d)", VOR_MAX_R);
+  cudaStream_t st = (cudaStream_t)stream;
+  VoronoiArgs v;
+  memset(&v, 0, sizeof(v));
+  v.R = R; v.H = H; v.W = W; v.weighted = region_weights != nullptr;
+  v.label = reinterpret_cast<uint8_t*>(scratch);                        // scratch: H*W bytes of labels, then R*H*W floats
+  float* tmp = scratch + ((size_t)H * W + 3) / 4;
+  double wsum = 0.0;
+  for (int i = 0; i < R && region_weights; ++i) wsum += region_weights[i];
+  for (int i = 0; i < R; ++i) {
+    v.px[i] = points_xy[2 * i]; v.py[i] = points_xy[2 * i + 1];
+    // norm_weights = w * count / total; effective_dist = dist / (sqrt(weight) + 1e-6)   (region_blend.py:205-219)
+    v.inv_w[i] = region_weights ? (float)(sqrt(region_weights[i] * R / wsum) + 1e-6) : 0.f;
+  }
+  CUDA_TRY(launch_voronoi_label(v, st));
+  BlurArgs b;
+  memset(&b, 0, sizeof(b));
+  b.R = R; b.H = H; b.W = W;
+  if (feather <= 0) {                                                    // feather_mask returns the hard mask
+    b.k = 1; b.w[0] = 1.f;
+  } else {
+    const float sigma = (float)feather / 3.0f;                           // 3-sigma rule (region_blend.py:101)
+    int k = (int)(6 * sigma + 1);
+    if (k % 2 == 0) ++k;
+    k = std::max(3, k);
+    if (k > BLUR_MAX_K) return fail(NST_ERR_INVALID, "voronoi_masks: feather %d needs a %d-tap kernel (max %d)", feather, k, BLUR_MAX_K);
+    if (k / 2 >= H || k / 2 >= W) return fail(NST_ERR_INVALID, "voronoi_masks: reflect padding %d needs a frame larger than %dx%d", k / 2, W, H);
+    float sum = 0.f;
+    for (int t = 0; t < k; ++t) { const float x = (float)(t - k / 2); b.w[t] = expf(-(x * x) / (2 * sigma * sigma)); sum += b.w[t]; }
+    for (int t = 0; t < k; ++t) b.w[t] /= sum;
+    b.k = k;
+  }
+  b.label = v.label; b.src = nullptr; b.dst = tmp; b.vertical = 0;
+  CUDA_TRY(launch_blur_pass(b, st));
+  b.label = nullptr; b.src = tmp; b.dst = masks; b.vertical = 1;
+  CUDA_TRY(launch_blur_pass(b, st));
   return NST_OK;
 }
 

@@ -358,4 +358,75 @@ cudaError_t launch_flow_ema(const FlowEmaArgs& a, cudaStream_t stream) {
   return cudaGetLastError();
 }
 
+// ---------------------------------------------------------------------------------------------
+// region masks: Voronoi cells + Gaussian feather (region_blend.py:69-102, 174-236)
+// ---------------------------------------------------------------------------------------------
+// label(y, x) = argmin_i sqrt((x - px_i)^2 + (y - py_i)^2) / (sqrt(weight_i) + 1e-6)   (first minimum wins, like torch.argmin);
+// mask_i = feather(label == i): reflect-padded Gaussian blur, sigma = feather / 3, kernel int(6 sigma + 1) made odd.  The reference
+// convolves with the 2-D outer-product kernel; the separable form here sums the same products in another order (|diff| ~ 1e-6).
+constexpr int VOR_MAX_R = 16, BLUR_MAX_K = 255;
+struct VoronoiArgs {
+  float px[VOR_MAX_R], py[VOR_MAX_R], inv_w[VOR_MAX_R];   // inv_w = 1 / (sqrt(weight) + 1e-6), or 0 = unweighted
+  int R, H, W, weighted;
+  uint8_t* label;           // [H,W]
+};
+__global__ void __launch_bounds__(256) voronoi_label_kernel(const __grid_constant__ VoronoiArgs a) {
+  const int hw = a.H * a.W;
+  for (int pix = blockIdx.x * blockDim.x + threadIdx.x; pix < hw; pix += gridDim.x * blockDim.x) {
+    const int y = pix / a.W, x = pix - y * a.W;
+    float best = INFINITY; int bi = 0;
+    for (int i = 0; i < a.R; ++i) {
+      const float dx = __fsub_rn((float)x, a.px[i]), dy = __fsub_rn((float)y, a.py[i]);
+      float d = __fsqrt_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)));
+      if (a.weighted) d = __fdiv_rn(d, a.inv_w[i]);          // inv_w holds sqrt(weight) + 1e-6 in the weighted case
+      if (d < best) { best = d; bi = i; }
+    }
+    a.label[pix] = (uint8_t)bi;
+  }
+}
+struct BlurArgs {
+  const uint8_t* label;     // horizontal pass input (label == r is the hard mask), or null
+  const float* src;         // vertical pass input [R,H,W]
+  float* dst;               // [R,H,W]
+  int R, H, W, k, vertical;
+  float w[BLUR_MAX_K];
+};
+__device__ __forceinline__ int reflect_idx(int i, int n) {        // F.pad(mode='reflect'): -1 -> 1, n -> n - 2
+  if (i < 0) i = -i;
+  if (i >= n) i = 2 * (n - 1) - i;
+  return i;
+}
+__global__ void __launch_bounds__(256) blur_pass_kernel(const __grid_constant__ BlurArgs a) {
+  const size_t hw = (size_t)a.H * a.W, total = hw * a.R;
+  const int pad = a.k / 2;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const int r = (int)(i / hw);
+    const int pix = (int)(i - (size_t)r * hw);
+    const int y = pix / a.W, x = pix - y * a.W;
+    float acc = 0.f;
+    if (!a.vertical) {
+      for (int t = 0; t < a.k; ++t) {
+        const int xx = reflect_idx(x + t - pad, a.W);
+        acc = fmaf(a.w[t], a.label[(size_t)y * a.W + xx] == r ? 1.f : 0.f, acc);
+      }
+    } else {
+      const float* pl = a.src + (size_t)r * hw;
+      for (int t = 0; t < a.k; ++t) {
+        const int yy = reflect_idx(y + t - pad, a.H);
+        acc = fmaf(a.w[t], pl[(size_t)yy * a.W + x], acc);
+      }
+    }
+    a.dst[i] = acc;
+  }
+}
+cudaError_t launch_voronoi_label(const VoronoiArgs& a, cudaStream_t stream) {
+  voronoi_label_kernel<<<std::min((a.H * a.W + 255) / 256, 148 * 16), 256, 0, stream>>>(a);
+  return cudaGetLastError();
+}
+cudaError_t launch_blur_pass(const BlurArgs& a, cudaStream_t stream) {
+  const size_t total = (size_t)a.R * a.H * a.W;
+  blur_pass_kernel<<<(int)std::min<size_t>((total + 255) / 256, (size_t)148 * 16), 256, 0, stream>>>(a);
+  return cudaGetLastError();
+}
+
 }  // namespace nst

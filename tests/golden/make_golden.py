@@ -148,6 +148,15 @@ def main():
     np.savez_compressed(os.path.join(HERE, "composite_crops_180x240.npz"), **pack)
     print("composite_from_crops:", float(out_o.mean()), float(out_n.mean()), "gap px", int((sum(m for m in masks) < 0.1).sum()))
 
+    # (2b) the C5 benchmark masks: generate_region_masks(1080, 1920, "voronoi", 4, seed=42, feather=20) (pipeline.py:1126-1127,1152) --
+    #      per-mask sums, 8192 sampled values (positions seeded) and the hard labels' histogram; the full masks would be 33 MB
+    big = rb.generate_region_masks(1080, 1920, "voronoi", 4, seed=42, feather=20)
+    big = torch.cat([m.reshape(1, 1080, 1920) for m in big])
+    pos = torch.randint(0, 1080 * 1920, (8192,), generator=torch.Generator().manual_seed(1))
+    np.savez_compressed(os.path.join(HERE, "voronoi4_1080p_samples.npz"), sums=big.double().sum((1, 2)).numpy(), pos=pos.numpy(),
+                        values=big.reshape(4, -1)[:, pos].numpy(), argmax_hist=torch.bincount(big.argmax(0).flatten(), minlength=4).numpy())
+    print("voronoi 1080p sums", big.double().sum((1, 2)).tolist())
+
     # (3) flow-guided EMA: the reference's `_warp_with_flow` (pipeline.py:425-439) + the lerp of :1927-1929
     import importlib.util
     spec = importlib.util.spec_from_file_location("ref_pipeline", os.path.join(REF, "pipeline.py"))

@@ -206,3 +206,22 @@ def test_multi_gpu_pipeline_one_process():
     mg = m.MultiGpuFramePipeline(factory, "raw_255", devices=devices, chunk=4)
     assert torch.equal(mg(frames), want)
     assert torch.equal(mg(frames[:1]), want[:1])                       # fewer frames than workers
+
+
+def test_voronoi_masks_match_the_reference_generator():
+    """generate_region_masks(..., "voronoi", 4, seed=42, feather=...) (region_blend.py:925, 174-236): same host RNG sequence for the seed
+    points, labelling + reflect-padded Gaussian feather on the device.  The reference convolves with the 2-D outer-product kernel
+    (1681 taps at feather 20), the device with the separable form: fp32 summation order differs, tolerance 2e-5."""
+    import neuralstyletransferv1_b200 as m
+    g = np.load(os.path.join(GOLDEN, "composite_voronoi4_48x64.npz"))
+    got = m.voronoi_masks(48, 64, 4, seed=42, feather=4).cpu()
+    assert float((got - torch.from_numpy(g["masks"])).abs().max()) <= 2e-5
+    s = np.load(os.path.join(GOLDEN, "voronoi4_1080p_samples.npz"))
+    big = m.voronoi_masks(1080, 1920, 4, seed=42, feather=20)
+    vals = big.reshape(4, -1)[:, torch.from_numpy(s["pos"]).cuda()].cpu().numpy()
+    assert np.abs(vals - s["values"]).max() <= 2e-5
+    assert np.allclose(big.double().sum((1, 2)).cpu().numpy(), s["sums"], rtol=1e-6)
+    assert np.array_equal(torch.bincount(big.argmax(0).flatten(), minlength=4).cpu().numpy(), s["argmax_hist"])
+    assert float((big.sum(0) - 1).abs().max()) <= 1e-4          # the cells partition the frame
+    hard = m.voronoi_masks(48, 64, 4, seed=42, feather=0).cpu()
+    assert set(hard.unique().tolist()) == {0.0, 1.0} and torch.equal(hard.sum(0), torch.ones(48, 64))
