@@ -266,7 +266,14 @@ __device__ __forceinline__ float2 unpack2(uint32_t u, int is_bf16) {
 }
 
 struct TileCoord { int n, ty0, tx0; };
+// `tile` is the CTA's position in the launch-wide sequence: CTA b visits b, b + G, b + 2G, ... (G = grid size).  Inside every FULL round
+// of G tiles the positions are rotated by round * rr_rot, so a CTA does not meet the same tile row / column every round when G and
+// the tile grid resonate (NST trunk: 37 tile rows, G = 148 = 4 * 37 -- the CTAs that owned the border rows finished 37 % late).
 __device__ __forceinline__ TileCoord decode_tile(const TcPlan& t, int tile) {
+  if (t.rr_rot) {
+    const int G = (int)gridDim.x, round = tile / G;
+    if ((round + 1) * G <= t.num_tiles) tile = round * G + (tile - round * G + round * t.rr_rot) % G;
+  }
   const int per_img = t.tiles_x * t.tiles_y;
   TileCoord c;
   c.n = tile / per_img;

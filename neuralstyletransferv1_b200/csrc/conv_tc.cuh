@@ -40,6 +40,7 @@ struct TcPlan {
   int a_stages, b_stages;
   int prod_warps;           // operand-producer warps that take part (the rest of TC_PROD_WARPS exit at once)
   int rr_tiles;             // CTA b takes tiles b, b + grid, b + 2*grid, ... instead of one contiguous run
+  int rr_rot;               // ... with the positions of full round i rotated by i * rr_rot (chosen on the host to balance border tiles)
   int epi_groups;           // 1, or 2 on epilogue-bound TMA-fed layers: warps 6-9 form a second epilogue group that drains the odd tiles of
                             // the CTA's run (accumulator buffer 1) while warps 2-5 drain the even ones; the transform then has <= 5 warps
   uint32_t epi_scratch_bytes;   // shared-memory scratch of ONE epilogue group (fold ring, or per-warp double channel statistics)

@@ -122,6 +122,7 @@ struct StatsFinalizeArgs {
   const float* gamma;       // [C]
   const float* beta;        // [C]
   float2* coeff;            // [N][C]
+  int rot;                  // round-robin assignment: positions of full round i are rotated by i * rot (TcPlan::rr_rot)
   int rr;                   // tile -> CTA assignment of the producing launch: 1 = CTA b takes tiles b, b + parts, ...; 0 = contiguous runs
   int parts, groups, N, C;  // part table [parts * groups][N][C][2]: slot (CTA b, epilogue group g) = b * groups + g
   int tiles_per_img;        // tiles of one sample; CTA b owns tiles [b*T/parts, (b+1)*T/parts), T = N * tiles_per_img; its group g drains
@@ -142,7 +143,20 @@ __global__ void __launch_bounds__(128) stats_finalize_kernel(const __grid_consta
     const int T = a.N * a.tiles_per_img, lo = n * a.tiles_per_img, hi = lo + a.tiles_per_img;
     for (int b = lane; b < a.parts; b += 32) {
       int from, to;                        // [from, to): indices i of CTA b's tile sequence that fall into sample n
-      if (a.rr) {                          // CTA b drains tiles b + i * parts
+      if (a.rr && a.rot) {                 // round i: tile i*parts + (b + i*rot) % parts (identity in the last, partial round)
+        for (int g = 0; g < a.groups; ++g) {
+          bool seen = false;
+          for (int r = lo / a.parts; r <= (hi - 1) / a.parts && !seen; ++r) {
+            if (r % a.groups != g) continue;
+            const int tl = (r + 1) * a.parts <= T ? r * a.parts + (b + r * a.rot) % a.parts : r * a.parts + b;
+            seen = tl >= lo && tl < hi && tl < T;
+          }
+          if (!seen) continue;
+          const double* st = a.part + ((((size_t)b * a.groups + g) * a.N + n) * a.C + c) * 2;
+          s1 += st[0]; s2 += st[1];
+        }
+        continue;
+      } else if (a.rr) {                   // CTA b drains tiles b + i * parts
         from = lo > b ? (lo - b + a.parts - 1) / a.parts : 0;
         to = hi > b ? (hi - b + a.parts - 1) / a.parts : 0;
       } else {                             // CTA b drains tiles [b*T/parts, (b+1)*T/parts)
@@ -172,11 +186,11 @@ __global__ void __launch_bounds__(128) stats_finalize_kernel(const __grid_consta
   a.coeff[i] = make_float2(scale, a.beta[c] - (float)mean * scale);
 }
 
-cudaError_t launch_stats_finalize(const double* part, int parts, int groups, int rr, int N, int C, int tiles_per_img, double inv_count,
+cudaError_t launch_stats_finalize(const double* part, int parts, int groups, int rr, int rot, int N, int C, int tiles_per_img, double inv_count,
                                   const float* gamma, const float* beta, float2* coeff, cudaStream_t stream) {
   StatsFinalizeArgs a;
   a.part = part; a.gamma = gamma; a.beta = beta; a.coeff = coeff;
-  a.parts = parts; a.groups = groups; a.rr = rr; a.N = N; a.C = C; a.tiles_per_img = tiles_per_img; a.inv_count = inv_count;
+  a.parts = parts; a.groups = groups; a.rr = rr; a.rot = rot; a.N = N; a.C = C; a.tiles_per_img = tiles_per_img; a.inv_count = inv_count;
   stats_finalize_kernel<<<(N * C + 3) / 4, 128, 0, stream>>>(a);
   return cudaGetLastError();
 }

@@ -29,7 +29,7 @@ struct CompositeArgs {
   float w[COMP_MAX_R * COMP_MAX_J];
 };
 cudaError_t launch_composite(const CompositeArgs& a, bool u8, cudaStream_t stream);
-cudaError_t launch_stats_finalize(const double* part, int parts, int groups, int rr, int N, int C, int tiles_per_img, double inv_count,
+cudaError_t launch_stats_finalize(const double* part, int parts, int groups, int rr, int rot, int N, int C, int tiles_per_img, double inv_count,
                                   const float* gamma, const float* beta, float2* coeff, cudaStream_t stream);
 // postproc.cu
 struct ResizePackArgs {
@@ -226,6 +226,7 @@ struct LayerPlan {
   // tensor maps of the TMA-fed operand path, encoded for `maps_ws` (re-encoded when the caller's workspace moves)
   CUtensorMap tmap[4], tmap_res;
   const void* maps_ws = nullptr;
+  std::map<int, int> rot_cache;      // frames in the launch -> rotation of the round-robin tile sequence (pick_rotation)
 };
 
 struct BufDims { int C = 0, H = 0, W = 0; size_t off = 0; size_t bytes = 0; };   // off / bytes per frame
@@ -1077,6 +1078,31 @@ static int encode_layer_maps(LayerPlan& lp, const ConvParams& p, const void* src
   return NST_OK;
 }
 
+// Rotation of the round-robin tile sequence (decode_tile in conv_tc.cu): simulate the per-CTA cost (border tiles run a second pass
+// in the transform and store less) for a few rotations and keep the flattest.  Deterministic in (tiling, batch, grid).
+static int pick_rotation(const TcPlan& t, int n_frames, int G) {
+  if (getenv("NST_NO_ROT")) return 0;
+  const int per_img = t.tiles_x * t.tiles_y, T = per_img * n_frames;
+  if (G < 2 || T < 2 * G) return 0;
+  static const int cand[] = {0, 1, 7, 13, 29, 41, 53, 61, 71, 89, 97, 113};
+  int best = 0; long best_cost = -1;
+  std::vector<int> cost(G);
+  for (int rot : cand) {
+    if (rot >= G) break;
+    std::fill(cost.begin(), cost.end(), 0);
+    for (int v = 0; v < T; ++v) {
+      const int round = v / G, b = v - round * G;
+      const int tile = (round + 1) * G <= T ? round * G + (b + round * rot) % G : v;
+      const int r = tile % per_img, tx = r / t.tiles_y, ty = r - tx * t.tiles_y;
+      const bool border = tx == 0 || ty == 0 || tx == t.tiles_x - 1 || ty == t.tiles_y - 1;
+      cost[b] += border ? 3 : 2;
+    }
+    const long mx = *std::max_element(cost.begin(), cost.end());
+    if (best_cost < 0 || mx < best_cost) { best_cost = mx; best = rot; }
+  }
+  return best;
+}
+
 static void print_tcprof(nst_handle* h, int n_frames) {
   std::vector<unsigned long long> all(64 * 16 + 64 * 2 * 148);
   if (cudaMemcpy(all.data(), h->prof_dev, all.size() * sizeof(unsigned long long), cudaMemcpyDeviceToHost) != cudaSuccess) return;
@@ -1169,7 +1195,7 @@ static int run_forward(nst_handle* h, const IoSpec& io, int N, int H, int W, voi
         p.out = buf(s.out);
         p.out_part = (double*)(stats + lp.part_off);
       }
-      int parts = 1, groups = 1, tiles_per_img = 0;
+      int parts = 1, groups = 1, tiles_per_img = 0, rot = 0;
       if (lp.use_tc) {
         TcArgs a;
         a.p = p; a.t = lp.t;
@@ -1186,6 +1212,12 @@ static int run_forward(nst_handle* h, const IoSpec& io, int N, int H, int W, voi
           memset(a.tmap, 0, sizeof(a.tmap)); memset(&a.tmap_res, 0, sizeof(a.tmap_res));
         }
         parts = conv_tc_grid(a.t, a.t.num_tiles, h->num_sms);
+        if (a.t.rr_tiles) {                                    // cached per micro-batch size: the simulation is host work
+          auto it = lp.rot_cache.find(n);
+          if (it == lp.rot_cache.end()) it = lp.rot_cache.emplace(n, pick_rotation(lp.t, n, parts)).first;
+          rot = it->second;
+        }
+        a.t.rr_rot = rot;
         groups = lp.t.epi_groups;
         tiles_per_img = lp.t.tiles_x * lp.t.tiles_y;
         for (int part = 0; part < d.nsplit; ++part) {
@@ -1205,7 +1237,7 @@ static int run_forward(nst_handle* h, const IoSpec& io, int N, int H, int W, voi
         // fold the per-CTA partial statistics into the (scale, shift) the consumer applies (its gamma / beta belong to the norm in between)
         if (lp.consumer < 0) return fail(NST_ERR_STATE, "internal: layer %s has no consumer", s.name.c_str());
         const LayerDev& cd = h->dev[lp.consumer];
-        CUDA_TRY(launch_stats_finalize(p.out_part, parts, groups, lp.use_tc ? lp.t.rr_tiles : 0, n, s.cout, tiles_per_img, 1.0 / ((double)lp.out_H * lp.out_W), cd.in_gamma, cd.in_beta,
+        CUDA_TRY(launch_stats_finalize(p.out_part, parts, groups, lp.use_tc ? lp.t.rr_tiles : 0, lp.use_tc ? rot : 0, n, s.cout, tiles_per_img, 1.0 / ((double)lp.out_H * lp.out_W), cd.in_gamma, cd.in_beta,
                                        (float2*)(stats + lp.coeff_off), stream));
         ++h->launches;
       }
