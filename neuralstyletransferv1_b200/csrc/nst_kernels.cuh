@@ -110,6 +110,15 @@ __device__ __forceinline__ void norm_coeff(const ConvParams& p, int n, int c, fl
   scale = cf.x; shift = cf.y;
 }
 
+// float(u8) / 255.0f, correctly rounded (ToTensor, pipeline.py:1099) in three instructions instead of a division: q = k * fl(1/255),
+// one Newton correction with the exact remainder.  Bit-identical to the IEEE division for every k in 0..255 (checked exhaustively,
+// tests/test_oracle.py::test_u8_to_unit_shortcut_is_exact).
+__device__ __forceinline__ float u8_to_unit(float k) {
+  const float r = __uint_as_float(0x3b808081u);          // fl32(1 / 255)
+  const float q = __fmul_rn(k, r);
+  return fmaf(fmaf(-q, 255.0f, k), r, q);
+}
+
 // Final image epilogue shared by both conv kernels: v[0..2] are the three net outputs (+bias).
 // Byte work: every step is the reference's own fp32 operation, individually rounded (no FMA contraction, true
 // division), so the uint8 result is bit-identical to pipeline.py:1451-1486 -> :2040-2043 -> :2089-2092 -> ToPILImage
@@ -147,7 +156,7 @@ __device__ __forceinline__ void store_image(const ConvParams& p, int n, int oy, 
     float o01 = __fadd_rn(__fmul_rn(__fdiv_rn(y, p.out_div[c]), p.out_scale[c]), p.out_shift[c]);
     o01 = fminf(fmaxf(o01, 0.f), 1.f);
     if (p.orig != nullptr) {
-      const float og = __fdiv_rn((float)p.orig[pix * 3 + c], 255.0f);        // ToTensor (pipeline.py:1099)
+      const float og = u8_to_unit((float)p.orig[pix * 3 + c]);                // ToTensor (pipeline.py:1099)
       if (p.mask != nullptr) {                                               // mask alpha-composite (pipeline.py:2040-2043)
         const float na = __fsub_rn(1.0f, a);
         o01 = (p.composite_mode == 0) ? __fadd_rn(__fmul_rn(a, o01), __fmul_rn(na, og)) : __fadd_rn(__fmul_rn(na, o01), __fmul_rn(a, og));

@@ -165,3 +165,17 @@ def test_bilinear_formula_used_by_the_kernels_is_torchs():
         top, bot = fma(bx(wx0), a, bx(wx1) * b), fma(bx(wx0), c, bx(wx1) * d)
         mine = fma(by(wy0), top, by(wy1) * bot)
         assert np.array_equal(mine, ref), (hi, wi, h, w)
+
+
+def test_u8_to_unit_shortcut_is_exact():
+    """csrc/nst_kernels.cuh::u8_to_unit: q = k * fl(1/255); q += fma(-q, 255, k) * fl(1/255) equals the IEEE fp32 division k / 255
+    (ToTensor) for all 256 byte values -- the multiply alone is wrong for 126 of them."""
+    k = np.arange(256, dtype=np.float32)
+    exact = (k / np.float32(255)).astype(np.float32)
+    r = np.frombuffer(np.uint32(0x3b808081).tobytes(), dtype=np.float32)[0]
+    assert r == np.float32(1) / np.float32(255)
+    fma = lambda a, b, c: (a.astype(np.float64) * np.float64(b) + c.astype(np.float64)).astype(np.float32)
+    q = (k * r).astype(np.float32)
+    assert int((q != exact).sum()) > 100
+    q2 = fma(fma(-q, 255.0, k), r, q)
+    assert np.array_equal(q2, exact)
