@@ -827,8 +827,8 @@ static int make_plan(nst_handle* h, int N, int H, int W) {
   for (int b = 0; b < NBUF; ++b) h->bufs[b] = BufDims();
   int producer[NBUF];
   for (int b = 0; b < NBUF; ++b) producer[b] = -1;
-  // who reads what: producer / consumer links and the element type of every activation tensor.  An error-compensated (F16X3)
-  // layer stores fp32 only when its consumer is error-compensated too, so plain fp16 layers always read fp16.
+  // who reads what: producer / consumer links and the element type of every activation tensor.  A tensor is fp32 exactly when its
+  // consumer is error-compensated (F16X3), so plain fp16 layers always read fp16.
   for (int li = 0; li < nl; ++li) {
     const LayerSpec& s = h->specs[li];
     LayerPlan& lp = h->plans[li];
@@ -843,7 +843,8 @@ static int make_plan(nst_handle* h, int N, int H, int W) {
     LayerPlan& lp = h->plans[li];
     const bool x3 = h->dev[li].prec == NST_PREC_F16X3;
     const bool cons_x3 = lp.consumer >= 0 && h->dev[lp.consumer].prec == NST_PREC_F16X3;
-    lp.out16 = h->act16 && !(x3 && cons_x3);
+    (void)x3;
+    lp.out16 = h->act16 && !cons_x3;          // an error-compensated consumer splits fp32 values into hi + lo: its source stays fp32
     if (h->precision == NST_PREC_F16X3 || h->precision == NST_PREC_FP32_DIRECT) lp.out16 = h->act16;
   }
   size_t stats_off = 0;
