@@ -131,7 +131,37 @@ struct StatsFinalizeArgs {
 };
 
 // One warp per (n, c): lane l adds the slots of CTAs l, l + 32, ... in index order, then a fixed butterfly joins the 32 lanes -- the
-// summation tree depends only on (parts, groups), never on scheduling.
+// summation tree depends only on (parts, groups), never on scheduling.  Which slots were written is decided first, for a batch of
+// CTAs at a time, so that the loads are independent and in flight together (this kernel sits between two dependent layers: the
+// first version chained ~10 L2 round trips per lane and took 9 us).
+__device__ __forceinline__ bool slot_written(const StatsFinalizeArgs& a, int b, int g, int lo, int hi, int T) {
+  if (a.rr && a.rot) {                   // round r: tile r*parts + (b + r*rot) % parts (identity in the last, partial round)
+    // sample n's tiles [lo, hi) span rounds r0..r1; every round strictly between them lies inside the sample, so CTA b has a
+    // tile there -- only the two boundary rounds need the membership test
+    const int r0 = lo / a.parts, r1 = (hi - 1) / a.parts;
+    const int ri = r0 + 1 + ((g - (r0 + 1)) % a.groups + a.groups) % a.groups;      // first interior round drained by group g
+    if (ri < r1) return true;
+    for (int k = 0; k < 2; ++k) {
+      const int r = k ? r1 : r0;
+      if (r % a.groups != g || (k && r1 == r0)) continue;
+      const int tl = (r + 1) * a.parts <= T ? r * a.parts + (b + r * a.rot) % a.parts : r * a.parts + b;
+      if (tl >= lo && tl < hi && tl < T) return true;
+    }
+    return false;
+  }
+  int from, to;                          // [from, to): indices i of CTA b's tile sequence that fall into sample n
+  if (a.rr) {                            // CTA b drains tiles b + i * parts
+    from = lo > b ? (lo - b + a.parts - 1) / a.parts : 0;
+    to = hi > b ? (hi - b + a.parts - 1) / a.parts : 0;
+  } else {                               // CTA b drains tiles [b*T/parts, (b+1)*T/parts)
+    const int t0 = (int)((long long)b * T / a.parts), t1 = (int)((long long)(b + 1) * T / a.parts);
+    from = (lo > t0 ? lo : t0) - t0;
+    to = (hi < t1 ? hi : t1) - t0;
+  }
+  const int first = from + ((g - from) % a.groups + a.groups) % a.groups;      // epilogue group g drains the indices with i % groups == g
+  return first < to;
+}
+
 __global__ void __launch_bounds__(128) stats_finalize_kernel(const __grid_constant__ StatsFinalizeArgs a) {
   const int i = (int)((blockIdx.x * blockDim.x + threadIdx.x) >> 5), lane = threadIdx.x & 31;
   if (i >= a.N * a.C) return;
@@ -141,35 +171,22 @@ __global__ void __launch_bounds__(128) stats_finalize_kernel(const __grid_consta
     if (lane == 0) { const double* st = a.part + ((size_t)n * a.C + c) * 2; s1 = st[0]; s2 = st[1]; }
   } else {
     const int T = a.N * a.tiles_per_img, lo = n * a.tiles_per_img, hi = lo + a.tiles_per_img;
-    for (int b = lane; b < a.parts; b += 32) {
-      int from, to;                        // [from, to): indices i of CTA b's tile sequence that fall into sample n
-      if (a.rr && a.rot) {                 // round i: tile i*parts + (b + i*rot) % parts (identity in the last, partial round)
-        for (int g = 0; g < a.groups; ++g) {
-          bool seen = false;
-          for (int r = lo / a.parts; r <= (hi - 1) / a.parts && !seen; ++r) {
-            if (r % a.groups != g) continue;
-            const int tl = (r + 1) * a.parts <= T ? r * a.parts + (b + r * a.rot) % a.parts : r * a.parts + b;
-            seen = tl >= lo && tl < hi && tl < T;
-          }
-          if (!seen) continue;
-          const double* st = a.part + ((((size_t)b * a.groups + g) * a.N + n) * a.C + c) * 2;
-          s1 += st[0]; s2 += st[1];
+    constexpr int KB = 5, KG = 2;          // CTAs per lane and epilogue groups per batch: 5 * 32 = 160 >= 148 SMs in one batch
+    for (int b0 = lane; b0 < a.parts; b0 += 32 * KB) {
+      double2 v[KB][KG];
+#pragma unroll
+      for (int k = 0; k < KB; ++k)
+#pragma unroll
+        for (int g = 0; g < KG; ++g) {
+          const int b = b0 + 32 * k;
+          v[k][g] = make_double2(0.0, 0.0);
+          if (b < a.parts && g < a.groups && slot_written(a, b, g, lo, hi, T))
+            v[k][g] = *reinterpret_cast<const double2*>(a.part + ((((size_t)b * a.groups + g) * a.N + n) * a.C + c) * 2);
         }
-        continue;
-      } else if (a.rr) {                   // CTA b drains tiles b + i * parts
-        from = lo > b ? (lo - b + a.parts - 1) / a.parts : 0;
-        to = hi > b ? (hi - b + a.parts - 1) / a.parts : 0;
-      } else {                             // CTA b drains tiles [b*T/parts, (b+1)*T/parts)
-        const int t0 = (int)((long long)b * T / a.parts), t1 = (int)((long long)(b + 1) * T / a.parts);
-        from = (lo > t0 ? lo : t0) - t0;
-        to = (hi < t1 ? hi : t1) - t0;
-      }
-      for (int g = 0; g < a.groups; ++g) { // epilogue group g drains the indices with i % groups == g
-        const int first = from + ((g - from) % a.groups + a.groups) % a.groups;
-        if (first >= to) continue;         // that group never saw sample n: slot unwritten
-        const double* st = a.part + ((((size_t)b * a.groups + g) * a.N + n) * a.C + c) * 2;
-        s1 += st[0]; s2 += st[1];
-      }
+#pragma unroll
+      for (int k = 0; k < KB; ++k)
+#pragma unroll
+        for (int g = 0; g < KG; ++g) { s1 += v[k][g].x; s2 += v[k][g].y; }
     }
   }
 #pragma unroll
