@@ -1209,6 +1209,39 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
     const int my_chan = ((lane & 16) ? 8 : 0) + ((lane & 8) ? 4 : 0) + ((lane & 4) ? 2 : 0) + ((lane & 2) ? 1 : 0);
     if (t.swap_ab) {
       epilogue_swap(args, tmem_base, ACC_FULL(0), ACC_EMPTY(0), first_tile, tile_step, end_tile, quad, lane, eg, EG);
+    } else if (t.fold_s == 2) {
+      // Image layer with the horizontal taps folded into N, pitch 32:  TMEM row m holds T[m][s*3+co] = sum_{r,ci} in[m + r*32][ci] w[co][ci][r][s]
+      // and out[m][co] = sum_s T[m + s][s*3 + co].  A warp's 32 rows are exactly one tile row (tx = lane) and only tx < TW <= 24 is an
+      // output, so row m + s is lane + s of the same warp: the sum is 24 shuffles, no shared memory and no barrier.
+      const float b0 = p.bias[0], b1 = p.bias[1], b2 = p.bias[2];
+      uint32_t it = (uint32_t)eg;
+      WaitProf wprof; wprof.init(args.prof);
+      for (int tile = first_tile + eg * tile_step; tile < ((t.dbg & 32) ? 0 : end_tile); tile += EG * tile_step, it += EG) {
+        const TileCoord tc = decode_tile(t, tile);
+        const uint32_t buf = it & 1u;
+        mbar_wait_warp(ACC_FULL(buf), (it >> 1) & 1u, err, 5, wprof);
+        tc_fence_after();
+        const int ox = tc.tx0 + lane;
+        const bool col_ok = lane < t.TW && ox < p.Wo;
+        for (int mb = 0; mb < t.MB; ++mb) {
+          const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + buf * (uint32_t)(t.MB * t.NPAD) + (uint32_t)(mb * t.NPAD);
+          uint32_t v[32];
+          tmem_ld32_nowait(taddr, v);
+          tmem_ld_wait();
+          if (mb == t.MB - 1) { tc_fence_before(); mbar_arrive_warp(ACC_EMPTY(buf)); }
+          float a0 = b0 + __uint_as_float(v[0]), a1 = b1 + __uint_as_float(v[1]), a2 = b2 + __uint_as_float(v[2]);
+#pragma unroll
+          for (int sx = 1; sx < 9; ++sx) {
+            a0 += __shfl_down_sync(0xffffffffu, __uint_as_float(v[3 * sx]), sx);
+            a1 += __shfl_down_sync(0xffffffffu, __uint_as_float(v[3 * sx + 1]), sx);
+            a2 += __shfl_down_sync(0xffffffffu, __uint_as_float(v[3 * sx + 2]), sx);
+          }
+          const int ty = mb * 4 + quad;                  // 128 rows of an M block = 4 tile rows of 32 positions
+          const int oy = tc.ty0 + ty;
+          if (col_ok && ty < t.TH && oy < p.Ho) store_image(p, tc.n, oy, ox, a0, a1, a2);
+        }
+      }
+      wprof.flush(2, warp == TC_FIRST_EPI_WARP && lane == 0);
     } else if (t.fold_s) {
       // Image layer with the horizontal taps folded into N:  TMEM holds T[m][s*3+co] = sum_{r,ci} in[m + r*P][ci] w[co][ci][r][s];
       // out[m][co] = sum_s T[m + s][s*3 + co].  Rows are exchanged through a ring of 128 + 8 rows in shared memory (row R at

@@ -355,7 +355,9 @@ static void tc_plan_static_(const LayerSpec& s, int precision, TcPlan& t) {
   // first layer (3 channels): a slot holds one pixel in 8 K positions (pair mode, K16 = 2 pixels, 3/8 useful) or two pixels
   // in 4 K positions each (quad mode, K16 = 4 pixels through LBO = 2 slots, 3/4 useful: 27 instead of 45 MMAs per M block)
   t.pair_mode = s.cin == 3 ? (getenv("NST_NO_QUAD") ? 1 : 2) : 0;
-  t.fold_s = (s.cout == 3 && s.ks == 9 && s.cin != 3 && !getenv("NST_NO_FOLD")) ? 1 : 0;
+  // fold_s: 2 = tile pitch fixed at 32 so that a warp's 32 accumulator rows are one tile row and the horizontal-tap sum is 24 warp
+  // shuffles (no shared-memory ring, no barriers); 1 = any pitch, rows exchanged through a ring (NST_FOLD_RING=1)
+  t.fold_s = (s.cout == 3 && s.ks == 9 && s.cin != 3 && !getenv("NST_NO_FOLD")) ? (getenv("NST_FOLD_RING") ? 1 : 2) : 0;
   if (t.fold_s) t.NPAD = 32;
   if (t.pair_mode) {
     t.CK = 8; t.planes = 1; t.nchunks = 1;
@@ -454,7 +456,7 @@ static bool tc_layout(const ConvParams& p, TcPlan& t, int MB, int bTH, int bTW, 
   // + per-sample norm coefficients [Cin<=256] + epilogue scratch: fold ring, or per-warp double channel statistics
   t.tbl_ints = tma ? 0 : 2 * (int)round_up((size_t)t.NPOS, 4);
   t.stat_ch = (int)round_up((size_t)(t.phase_mode ? t.NPAD / 4 : t.NPAD), 16);
-  t.epi_scratch_bytes = (uint32_t)(t.fold_s ? TC_FOLD_RING_BYTES : 4 * t.stat_ch * 16);
+  t.epi_scratch_bytes = (uint32_t)(t.fold_s == 1 ? TC_FOLD_RING_BYTES : (t.fold_s == 2 ? 0 : 4 * t.stat_ch * 16));
   const int bar_bytes = 704 + t.tbl_ints * 4 + 256 * 8 + t.epi_groups * (int)t.epi_scratch_bytes;
   const int avail = TC_SMEM_LIMIT - b_total - bar_bytes;
   const int a_stages = avail / (int)t.a_stage_bytes;
@@ -496,10 +498,14 @@ static bool tc_plan_geometry(const ConvParams& p, TcPlan& t, int force_TH = 0, i
     double mma_cyc = (double)MB * t.nchunks * t.nent * t.k16_per_ent * t.nterms * mma_one;
     if (t.phase_mode) mma_cyc = (double)MB * t.nchunks * t.k16_per_ent * (t.NPAD * (t.phase_mode == 1 ? 2.5 : 1.4));
     for (int TH = 1; TH <= std::min(64, M); ++TH) {
-      if (force_TH && TH != force_TH) continue;
+      if (force_TH && TH != force_TH && t.fold_s != 2) continue;      // (the pitch-32 image layer has one TH per MB)
       int P = M / TH;
       int TW = p.stride == 1 ? P - e : P - 1;
       if (TW < 1) continue;
+      if (t.fold_s == 2) {                     // pitch 32 exactly (TH = M / 32); a narrow image just leaves columns unused
+        if (P != 32 || TH * 32 != M) continue;
+        TW = std::min(TW, p.Wo);
+      } else
       if (TW > p.Wo) { TW = p.Wo; P = p.stride == 1 ? TW + e : TW + 1; }
       if (TW < 4 && p.Wo >= 4) continue;
       const int THe = std::min(TH, p.Ho);
