@@ -173,6 +173,36 @@ int nst_resize_post_pack_u8(const float* src01, int N, int Hi, int Wi, const uin
 int nst_voronoi_masks_f32(const float* points_xy, const float* region_weights, int R, int feather, float* masks, float* scratch,
                           int H, int W, void* stream);
 
+/* Replaces: the other generators of region_blend.generate_region_masks (region_blend.py:109-172, 307-521, 925-981) for scalars the host
+ * has drawn with the reference's `random.Random` sequence (neuralstyletransferv1_b200/region_masks.py: pattern_spec).
+ * mode 0 = rectangles (grid_masks, fractal_quad_masks): rects = R x (y1, y2, x1, x2) [host];
+ * mode 1 = diagonal (params6[0] = 1: x + y, 0: (W-1-x) + y), 2 = radial (cx, cy, rotation), 3 = waves (frequency, amplitude,
+ * direction 0/1/2 = horizontal / vertical / diagonal, phase), 4 = spiral (cx, cy, tightness, rotation, max(H, W)), 5 = concentric (cx, cy):
+ * a scalar field per pixel evaluated with the reference's fp32 operation sequence, normalised over the frame (norm 0 = none, 1 = divide by
+ * the maximum, 2 = (v - min) / (max - min + 1e-6)), then mask_i = feather(lo[i] <= field < hi[i]); params6 / lo / hi: [host] fp32.
+ * masks: [dev] fp32 [R,H,W]; scratch: [dev] nst_mask_scratch_floats(R, H, W) floats.  atan2f / sinf are the device's (<= 2 ulp from the
+ * host's): a pixel whose field lies within an ulp of a band edge may land in the neighbouring band. */
+int nst_pattern_masks_f32(int mode, int norm, const float* params6, const float* lo, const float* hi, const int* rects, int R, int feather,
+                          float* masks, float* scratch, int H, int W, void* stream);
+
+/* Replaces: region_blend.rotate_all_masks (region_blend.py:25-66): every mask through cv2.warpAffine(getRotationMatrix2D((W/2, H/2), angle, 1),
+ * INTER_LINEAR, BORDER_REPLICATE) -- OpenCV's 1/1024 fixed-point coordinates rounded to 1/32 pixel, fp32 table weights, bit-exact -- and
+ * divided by the clamped sum of the rotated masks, in one pass.  masks / out: [dev] fp32 [R,H,W], not aliased. */
+int nst_rotate_masks_f32(const float* masks, float* out, int R, int H, int W, double angle_degrees, void* stream);
+
+/* Replaces: region_blend.warp_all_masks_organic / warp_mask_organic / _generate_flow_field / _simplex_noise_2d (region_blend.py:604-810).
+ * mode 0 = blob, 1 = tentacle, 2 = wave, 3 = pulse.  Region r is displaced by its own flow field (noise modes: two 2-octave sin / cos
+ * fields evaluated in double like numpy, min / max normalised over the frame; offsets: [host] 8 doubles per region = (offset_x, offset_y)
+ * of octave 0, 1 of the x field then of the y field, drawn by the host from numpy's default_rng like the reference) and resampled with
+ * cv2.remap(INTER_LINEAR, BORDER_REFLECT) arithmetic; pixels whose coverage sum is < 0.1 are filled by max-pool dilations 5 / 11 / 21 / 41
+ * (passes are skipped on the device once no gap is left); finally m / clamp(sum, 1e-6).  time_offset = frame_idx * speed * 0.02.
+ * masks / out: [dev] fp32 [R,H,W], not aliased; scratch: [dev] nst_mask_scratch_floats(R, H, W) floats. */
+int nst_warp_masks_organic_f32(const float* masks, float* out, int R, int H, int W, int mode, double amplitude, double frequency,
+                               double time_offset, const double* offsets, float* scratch, void* stream);
+
+/* Scratch (in floats) the two mask calls above need. */
+size_t nst_mask_scratch_floats(int R, int H, int W);
+
 /* ---- temporal post-processing --------------------------------------------------------------- */
 
 /* Replaces: `_warp_with_flow` + the flow-guided EMA lerp (pipeline.py:425-439, 1918-1931): warp the previous fused frame along the
@@ -180,6 +210,25 @@ int nst_voronoi_masks_f32(const float* points_xy, const float* region_weights, i
  * out = clip(alpha * curr + (1 - alpha) * warped, 0, 1).  All images [dev] fp32 HWC [H,W,3] in 0..1, flow [dev] fp32 [H,W,2] = (dx, dy);
  * alpha is clamped to [0,1].  out may alias curr, not prev.  (The flow estimate itself stays in OpenCV) */
 int nst_flow_ema_f32(const float* curr, const float* prev, const float* flow, float* out, int H, int W, double alpha, void* stream);
+
+/* Replaces: the LAB lightness / chroma EMA of pipeline.py:1938-1975 for N consecutive frames in one launch (each pixel's EMA is
+ * independent, so one thread carries its (L, a, b) state through the chunk).  frames / out: [dev] uint8 [N,H,W,3] RGB.  rgb2lab / lab2rgb:
+ * [dev] uint32 [2^24] tables of Pillow's `convert("LAB")` / `convert("RGB")` (index c0 << 16 | c1 << 8 | c2 -> c0' | c1' << 8 | c2' << 16),
+ * filled by the host from Pillow itself (neuralstyletransferv1_b200/temporal.py).  prev_L / prev_a / prev_b: [dev] fp32 [H,W] running
+ * state, read unless `init` (first frame of a clip: prev = current) and always written back.
+ *   L_sm = fp32(alpha) * L + fp32(1 - alpha) * prev_L;  prev_L = L_sm;  L8 = trunc(clip(L_sm, 0, 255));  same for a, b with chroma_alpha. */
+int nst_lab_ema_u8(const uint8_t* frames, uint8_t* out, int N, int H, int W, const uint32_t* rgb2lab, const uint32_t* lab2rgb,
+                   float* prev_L, float* prev_a, float* prev_b, int init, int smooth_lightness, int smooth_chroma,
+                   double smooth_alpha, double chroma_alpha, void* stream);
+
+/* Replaces: the motion-adaptive blend of pipeline.py:2072-2086 (MOTION_NORM / MIN_ALPHA / GAUSS_SIGMA of :1075-1077 are arguments):
+ *   m = cv2.GaussianBlur(clip(|flow| / motion_norm, 0, 1), (0, 0), sigma);  alpha = blend - (blend - min_alpha) * m;
+ *   out = trunc(clip(alpha * styled/255 + (1 - alpha) * original/255, 0, 1) * 255)
+ * with OpenCV's fp32 filter arithmetic (row pass: sequential FMA; column pass: symmetric pairs, FMA; scalar tails of the last W % 4 resp.
+ * W % 8 columns without FMA -- the AVX2 build's order).  styled / original / out: [dev] uint8 [H,W,3]; flow: [dev] fp32 [H,W,2];
+ * scratch: [dev] H*W floats. */
+int nst_motion_blend_u8(const uint8_t* styled, const uint8_t* original, const float* flow, uint8_t* out, float* scratch, int H, int W,
+                        double blend, double min_alpha, double motion_norm, double sigma, void* stream);
 
 /* ---- introspection ------------------------------------------------------------------------- */
 

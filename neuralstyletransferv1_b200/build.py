@@ -8,8 +8,8 @@ import subprocess
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "libb200nst.so")
-SOURCES = ["nst_api.cu", "conv_tc.cu", "conv_direct.cu", "elementwise.cu", "postproc.cu"]
-HEADERS = ["nst_kernels.cuh", "conv_tc.cuh", os.path.join("..", "..", "include", "b200nst.h")]
+SOURCES = ["nst_api.cu", "conv_tc.cu", "conv_direct.cu", "elementwise.cu", "postproc.cu", "masks.cu", "temporal.cu"]
+HEADERS = ["nst_kernels.cuh", "conv_tc.cuh", "api_util.cuh", "post_math.cuh", os.path.join("..", "..", "include", "b200nst.h")]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC", "-shared"]
 

@@ -12,6 +12,7 @@
 
 #include "../../include/b200nst.h"
 #include "conv_tc.cuh"
+#include "api_util.cuh"
 
 namespace nst {
 cudaError_t launch_conv_direct(const ConvParams& p, const float* wdir, cudaStream_t stream);
@@ -70,6 +71,14 @@ using namespace nst;
 static thread_local char g_err[512] = "";
 
 static int fail(int code, const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+  return code;
+}
+// the same, for the entry points that live in masks.cu / temporal.cu (api_util.cuh)
+int nst::api_fail(int code, const char* fmt, ...) {
   va_list ap;
   va_start(ap, fmt);
   vsnprintf(g_err, sizeof(g_err), fmt, ap);
@@ -1464,6 +1473,33 @@ extern "C" int nst_composite_from_crops_f32(int R, const int* bbox, const float*
   return NST_OK;
 }
 
+// mask_r = feather(label == r): feather_mask / gaussian_blur_mask (region_blend.py:69-102) as two separable reflect-padded passes.
+// label: [dev] H*W bytes (255 = no region); tmp: [dev] R*H*W floats.
+int nst::feather_labels(const uint8_t* label, int R, int feather, float* masks, float* tmp, int H, int W, cudaStream_t st, const char* who) {
+  BlurArgs b;
+  memset(&b, 0, sizeof(b));
+  b.R = R; b.H = H; b.W = W;
+  if (feather <= 0) {                                                    // feather_mask returns the hard mask
+    b.k = 1; b.w[0] = 1.f;
+  } else {
+    const float sigma = (float)feather / 3.0f;                           // 3-sigma rule (region_blend.py:101)
+    int k = (int)(6 * sigma + 1);
+    if (k % 2 == 0) ++k;
+    k = std::max(3, k);
+    if (k > BLUR_MAX_K) return fail(NST_ERR_INVALID, "%s: feather %d needs a %d-tap kernel (max %d)", who, feather, k, BLUR_MAX_K);
+    if (k / 2 >= H || k / 2 >= W) return fail(NST_ERR_INVALID, "%s: reflect padding %d needs a frame larger than %dx%d", who, k / 2, W, H);
+    float sum = 0.f;
+    for (int t = 0; t < k; ++t) { const float x = (float)(t - k / 2); b.w[t] = expf(-(x * x) / (2 * sigma * sigma)); sum += b.w[t]; }
+    for (int t = 0; t < k; ++t) b.w[t] /= sum;
+    b.k = k;
+  }
+  b.label = label; b.src = nullptr; b.dst = tmp; b.vertical = 0;
+  CUDA_TRY(launch_blur_pass(b, st));
+  b.label = nullptr; b.src = tmp; b.dst = masks; b.vertical = 1;
+  CUDA_TRY(launch_blur_pass(b, st));
+  return NST_OK;
+}
+
 extern "C" int nst_voronoi_masks_f32(const float* points_xy, const float* region_weights, int R, int feather, float* masks, float* scratch,
                                      int H, int W, void* stream) {
   if (!points_xy || !masks || !scratch || R < 1 || R > VOR_MAX_R || H < 2 || W < 2) return fail(NST_ERR_INVALID, "voronoi_masks: bad argument (1 <= R <= %d)", VOR_MAX_R);
@@ -1481,28 +1517,7 @@ extern "C" int nst_voronoi_masks_f32(const float* points_xy, const float* region
     v.inv_w[i] = region_weights ? (float)(sqrt(region_weights[i] * R / wsum) + 1e-6) : 0.f;
   }
   CUDA_TRY(launch_voronoi_label(v, st));
-  BlurArgs b;
-  memset(&b, 0, sizeof(b));
-  b.R = R; b.H = H; b.W = W;
-  if (feather <= 0) {                                                    // feather_mask returns the hard mask
-    b.k = 1; b.w[0] = 1.f;
-  } else {
-    const float sigma = (float)feather / 3.0f;                           // 3-sigma rule (region_blend.py:101)
-    int k = (int)(6 * sigma + 1);
-    if (k % 2 == 0) ++k;
-    k = std::max(3, k);
-    if (k > BLUR_MAX_K) return fail(NST_ERR_INVALID, "voronoi_masks: feather %d needs a %d-tap kernel (max %d)", feather, k, BLUR_MAX_K);
-    if (k / 2 >= H || k / 2 >= W) return fail(NST_ERR_INVALID, "voronoi_masks: reflect padding %d needs a frame larger than %dx%d", k / 2, W, H);
-    float sum = 0.f;
-    for (int t = 0; t < k; ++t) { const float x = (float)(t - k / 2); b.w[t] = expf(-(x * x) / (2 * sigma * sigma)); sum += b.w[t]; }
-    for (int t = 0; t < k; ++t) b.w[t] /= sum;
-    b.k = k;
-  }
-  b.label = v.label; b.src = nullptr; b.dst = tmp; b.vertical = 0;
-  CUDA_TRY(launch_blur_pass(b, st));
-  b.label = nullptr; b.src = tmp; b.dst = masks; b.vertical = 1;
-  CUDA_TRY(launch_blur_pass(b, st));
-  return NST_OK;
+  return feather_labels(v.label, R, feather, masks, tmp, H, W, st, "voronoi_masks");
 }
 
 extern "C" int nst_resize_post_pack_u8(const float* src01, int N, int Hi, int Wi, const uint8_t* original, const float* mask, double blend,

@@ -1,0 +1,111 @@
+// Temporal post-processing on the device, second part: the LAB lightness / chroma EMA and the motion-adaptive
+// blend that follow the flow-guided EMA of postproc.cu in the reference's per-frame loop.
+//
+//   lab_ema        pipeline.py:1938-1975.  Pillow's RGB <-> LAB conversion is littleCMS with interpolated 16-bit tables -- a pure
+//                  function of the uint8 triple, so the device reads it from two 2^24-entry tables the host fills ONCE by running
+//                  Pillow's own transform over all colours (neuralstyletransferv1_b200/temporal.py).  The EMA is independent per
+//                  pixel: one thread walks its pixel through a whole chunk of N frames with the running (L, a, b) state in
+//                  registers, so the state planes are read and written once per chunk instead of once per frame.
+//   motion_blend   pipeline.py:2072-2086.  alpha = blend - (blend - MIN_ALPHA) * GaussianBlur(clip(|flow| / MOTION_NORM, 0, 1), sigma 3),
+//                  out = pack(clip(alpha * styled + (1 - alpha) * original, 0, 1)).  Two launches: flow magnitude + row filter, then
+//                  column filter + blend + truncating pack.  cv2.GaussianBlur's fp32 operation order is documented in post_math.cuh.
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+
+#include "api_util.cuh"
+#include "post_math.cuh"
+
+namespace nst {
+using namespace pm;
+
+struct LabEmaArgs {
+  const uint8_t* frames; uint8_t* out;          // [N,H,W,3]
+  const uint32_t* rgb2lab; const uint32_t* lab2rgb;   // [2^24]: index (c0 << 16 | c1 << 8 | c2) -> c0' | c1' << 8 | c2' << 16
+  float* prev_L; float* prev_a; float* prev_b;  // [H,W] running state (in / out)
+  int N, H, W, init, smooth_L, smooth_ab;
+  float aL, aL_comp, aC, aC_comp;               // fp32(alpha), fp32(1 - alpha): numpy narrows the Python doubles against fp32 arrays
+};
+__global__ void __launch_bounds__(256) lab_ema_kernel(const __grid_constant__ LabEmaArgs a) {
+  const int hw = a.H * a.W;
+  for (int pix = blockIdx.x * blockDim.x + threadIdx.x; pix < hw; pix += gridDim.x * blockDim.x) {
+    LabState st = {0.f, 0.f, 0.f};
+    if (!a.init) {
+      if (a.smooth_L) st.L = a.prev_L[pix];
+      if (a.smooth_ab) { st.a = a.prev_a[pix]; st.b = a.prev_b[pix]; }
+    }
+    for (int n = 0; n < a.N; ++n) {
+      const uint8_t* px = a.frames + ((size_t)n * hw + pix) * 3;
+      const uint32_t lab = __ldg(a.rgb2lab + (((uint32_t)px[0] << 16) | ((uint32_t)px[1] << 8) | px[2]));
+      const uint32_t idx = lab_ema_step(lab, st, a.init && n == 0, a.smooth_L, a.smooth_ab, a.aL, a.aL_comp, a.aC, a.aC_comp);
+      const uint32_t rgb = __ldg(a.lab2rgb + idx);
+      uint8_t* o = a.out + ((size_t)n * hw + pix) * 3;
+      o[0] = (uint8_t)(rgb & 255u); o[1] = (uint8_t)((rgb >> 8) & 255u); o[2] = (uint8_t)((rgb >> 16) & 255u);
+    }
+    if (a.smooth_L) a.prev_L[pix] = st.L;
+    if (a.smooth_ab) { a.prev_a[pix] = st.a; a.prev_b[pix] = st.b; }
+  }
+}
+
+constexpr int MB_MAX_K = 63;
+struct MotionBlendArgs {
+  const uint8_t* styled; const uint8_t* original; const float* flow; uint8_t* out; float* rowf;   // rowf: [H,W] row-filtered motion
+  int H, W, k;
+  float norm_div;                     // MOTION_NORM
+  float max_alpha, alpha_span;        // fp32(blend), fp32(blend - MIN_ALPHA)
+  float kern[MB_MAX_K];
+};
+__global__ void __launch_bounds__(256) motion_row_kernel(const __grid_constant__ MotionBlendArgs a) {
+  const int hw = a.H * a.W;
+  for (int pix = blockIdx.x * blockDim.x + threadIdx.x; pix < hw; pix += gridDim.x * blockDim.x) {
+    const int y = pix / a.W, x = pix - y * a.W;
+    a.rowf[pix] = motion_row_at(a.flow, a.W, y, x, a.kern, a.k, a.norm_div);
+  }
+}
+__global__ void __launch_bounds__(256) motion_col_blend_kernel(const __grid_constant__ MotionBlendArgs a) {
+  const int hw = a.H * a.W;
+  for (int pix = blockIdx.x * blockDim.x + threadIdx.x; pix < hw; pix += gridDim.x * blockDim.x) {
+    const int y = pix / a.W, x = pix - y * a.W;
+    const float m = motion_col_at(a.rowf, a.H, a.W, y, x, a.kern, a.k);
+    motion_fuse(m, a.max_alpha, a.alpha_span, a.styled + (size_t)pix * 3, a.original + (size_t)pix * 3, a.out + (size_t)pix * 3);
+  }
+}
+
+static inline int grid_for(int hw) { return std::min((hw + 255) / 256, 148 * 16); }
+
+}  // namespace nst
+
+using namespace nst;
+
+extern "C" int nst_lab_ema_u8(const uint8_t* frames, uint8_t* out, int N, int H, int W, const uint32_t* rgb2lab, const uint32_t* lab2rgb,
+                              float* prev_L, float* prev_a, float* prev_b, int init, int smooth_lightness, int smooth_chroma,
+                              double smooth_alpha, double chroma_alpha, void* stream) {
+  if (!frames || !out || !rgb2lab || !lab2rgb || N < 1 || H < 1 || W < 1) return api_fail(NST_ERR_INVALID, "lab_ema: null / empty argument");
+  if ((smooth_lightness && !prev_L) || (smooth_chroma && (!prev_a || !prev_b))) return api_fail(NST_ERR_INVALID, "lab_ema: the enabled channels need their state planes");
+  LabEmaArgs a;
+  a.frames = frames; a.out = out; a.rgb2lab = rgb2lab; a.lab2rgb = lab2rgb; a.prev_L = prev_L; a.prev_a = prev_a; a.prev_b = prev_b;
+  a.N = N; a.H = H; a.W = W; a.init = init != 0; a.smooth_L = smooth_lightness != 0; a.smooth_ab = smooth_chroma != 0;
+  a.aL = (float)smooth_alpha; a.aL_comp = (float)(1.0 - smooth_alpha);
+  a.aC = (float)chroma_alpha; a.aC_comp = (float)(1.0 - chroma_alpha);
+  lab_ema_kernel<<<grid_for(H * W), 256, 0, (cudaStream_t)stream>>>(a);
+  NST_CUDA_TRY(cudaGetLastError());
+  return NST_OK;
+}
+
+extern "C" int nst_motion_blend_u8(const uint8_t* styled, const uint8_t* original, const float* flow, uint8_t* out, float* scratch, int H, int W,
+                                   double blend, double min_alpha, double motion_norm, double sigma, void* stream) {
+  if (!styled || !original || !flow || !out || !scratch || H < 1 || W < 1) return api_fail(NST_ERR_INVALID, "motion_blend: null / empty argument");
+  if (!(sigma > 0) || !(motion_norm > 0)) return api_fail(NST_ERR_INVALID, "motion_blend: sigma and motion_norm must be positive");
+  MotionBlendArgs a;
+  memset(&a, 0, sizeof(a));
+  const int k = gaussian_kernel_f32(sigma, a.kern, MB_MAX_K);
+  if (k == 0) return api_fail(NST_ERR_INVALID, "motion_blend: sigma %.2f needs more than %d taps", sigma, MB_MAX_K);
+  a.styled = styled; a.original = original; a.flow = flow; a.out = out; a.rowf = scratch; a.H = H; a.W = W; a.k = k;
+  a.norm_div = (float)motion_norm;
+  a.max_alpha = (float)blend; a.alpha_span = (float)(blend - min_alpha);
+  cudaStream_t st = (cudaStream_t)stream;
+  motion_row_kernel<<<grid_for(H * W), 256, 0, st>>>(a);
+  motion_col_blend_kernel<<<grid_for(H * W), 256, 0, st>>>(a);
+  NST_CUDA_TRY(cudaGetLastError());
+  return NST_OK;
+}

@@ -365,3 +365,200 @@ def flow_ema(curr01_hwc, prev01_hwc, flow_hw2, alpha: float):
     warped = cv2.remap(prev01_hwc, map_x, map_y, interpolation=cv2.INTER_LINEAR, borderMode=cv2.BORDER_REPLICATE)
     a = float(max(0.0, min(1.0, alpha)))
     return (a * curr01_hwc + (1.0 - a) * warped).clip(0.0, 1.0).astype("float32")
+
+
+# --------------------------------------------------------------------------- #
+# region masks: patterns, rotation, organic warp
+# --------------------------------------------------------------------------- #
+def gaussian_blur_mask(mask: Tensor, sigma: float) -> Tensor:
+    """region_blend.py:69-94: 2-D outer-product Gaussian, reflect padding."""
+    if sigma <= 0:
+        return mask
+    ks = int(6 * sigma + 1)
+    ks += ks % 2 == 0
+    ks = max(3, ks)
+    x = torch.arange(ks, dtype=torch.float32) - ks // 2
+    k1 = torch.exp(-x ** 2 / (2 * sigma ** 2))
+    k1 = k1 / k1.sum()
+    k2 = (k1.view(-1, 1) @ k1.view(1, -1)).view(1, 1, ks, ks)
+    return F.conv2d(F.pad(mask, (ks // 2,) * 4, mode="reflect"), k2)
+
+
+def feather_mask(mask: Tensor, feather_px: int) -> Tensor:
+    """region_blend.py:97-102."""
+    return mask if feather_px <= 0 else gaussian_blur_mask(mask, feather_px / 3.0)
+
+
+def pattern_masks(H: int, W: int, mode: str, count: int, seed: int, feather: int) -> Tensor:
+    """generate_region_masks for grid / diagonal / fractal / radial / waves / spiral / concentric (region_blend.py:109-172, 307-521,
+    925-981) as the reference's torch expressions; the random scalars come from the product's host helper `pattern_spec` (the same
+    `random.Random` draws -- pinned, like everything here, by the fixtures of tests/golden/make_golden_masks.py).  -> [count,H,W]."""
+    import math
+    import random
+    from neuralstyletransferv1_b200.region_masks import pattern_spec
+    rng = random.Random(seed)
+    if mode == "random":
+        mode = rng.choice(["grid", "diagonal", "voronoi", "fractal", "radial", "waves", "spiral", "concentric"])
+    sp = pattern_spec(H, W, mode, count, rng)
+    yy = torch.arange(H, dtype=torch.float32).view(H, 1).expand(H, W)
+    xx = torch.arange(W, dtype=torch.float32).view(1, W).expand(H, W)
+    hard = []
+    if mode in ("grid", "fractal"):
+        for (y1, y2, x1, x2) in sp.rects:
+            m = torch.zeros(H, W)
+            m[y1:y2, x1:x2] = 1.0
+            hard.append(m)
+    else:
+        if mode == "diagonal":
+            f = (xx + yy) if sp.p[0] else ((W - 1 - xx) + yy)
+            f = f / f.max()
+        elif mode == "radial":
+            f = (torch.atan2(yy - sp.p[1], xx - sp.p[0]) + math.pi + sp.p[2]) % (2 * math.pi)
+        elif mode == "waves":
+            yn, xn = yy / H, xx / W
+            t = (xn, yn, (xn + yn) / 2)[int(sp.p[2])]
+            pos = (yn, xn, t)[int(sp.p[2])] + torch.sin(t * sp.p[0] * 2 * math.pi + sp.p[3]) * sp.p[1]
+            f = (pos - pos.min()) / (pos.max() - pos.min() + 1e-6)
+        elif mode == "spiral":
+            yc, xc = yy - sp.p[1], xx - sp.p[0]
+            r = torch.sqrt(xc ** 2 + yc ** 2)
+            theta = torch.atan2(yc, xc) + math.pi + sp.p[3]
+            f = ((theta + r / max(H, W) * sp.p[2] * 2 * math.pi) % (2 * math.pi)) / (2 * math.pi)
+        elif mode == "concentric":
+            r = torch.sqrt((xx - sp.p[0]) ** 2 + (yy - sp.p[1]) ** 2)
+            f = r / r.max()
+        else:
+            raise ValueError(mode)
+        hard = [((f >= lo) & (f < hi)).float() for lo, hi in zip(sp.lo, sp.hi)]
+    masks = [feather_mask(m.view(1, 1, H, W), feather) for m in hard]
+    while len(masks) < count:
+        masks.append(masks[-1].clone())
+    return torch.cat([m.view(1, H, W) for m in masks[:count]])
+
+
+def rotate_all_masks(masks: Tensor, angle: float) -> Tensor:
+    """region_blend.py:25-66 with the reference's own OpenCV calls.  masks [R,H,W] -> [R,H,W]."""
+    import cv2
+    if angle == 0:
+        return masks
+    R, H, W = masks.shape
+    M = cv2.getRotationMatrix2D((W / 2, H / 2), angle, 1.0)
+    rot = [torch.from_numpy(cv2.warpAffine(m.numpy(), M, (W, H), flags=cv2.INTER_LINEAR, borderMode=cv2.BORDER_REPLICATE)) for m in masks]
+    s = torch.zeros_like(rot[0])
+    for m in rot:
+        s += m
+    s = s.clamp(min=1e-6)
+    return torch.stack([m / s for m in rot])
+
+
+def _simplex_noise_2d(H, W, frequency, octaves, seed, time_offset):
+    """region_blend.py:604-652."""
+    import numpy as np
+    rng = np.random.default_rng(seed)
+    xx, yy = np.meshgrid(np.linspace(0, frequency, W), np.linspace(0, frequency, H))
+    result = np.zeros((H, W), dtype=np.float32)
+    amplitude, total, fm = 1.0, 0.0, 1.0
+    for octave in range(octaves):
+        ox = time_offset * (0.5 + 0.3 * octave) + rng.random() * 1000
+        oy = time_offset * (0.3 + 0.2 * octave) + rng.random() * 1000
+        noise = np.sin(xx * fm + ox) * np.cos(yy * fm + oy)
+        noise += np.sin((xx + yy) * fm * 0.7 + ox * 0.8) * 0.5
+        noise += np.cos((xx - yy) * fm * 0.5 + oy * 0.6) * 0.3
+        result += noise * amplitude
+        total += amplitude
+        amplitude *= 0.5
+        fm *= 2.0
+    result = result / total
+    return (result - result.min()) / (result.max() - result.min() + 1e-6)
+
+
+def warp_all_masks_organic(masks: Tensor, mode: str, amplitude: float, frequency: float, speed: float, seed: int, frame_idx: int) -> Tensor:
+    """region_blend.py:655-810 (flow field, cv2.remap with BORDER_REFLECT, dilation gap fill, renormalisation).  masks [R,H,W]."""
+    import cv2
+    import numpy as np
+    R, H, W = masks.shape
+    t = frame_idx * speed * 0.02
+    warped = []
+    for i in range(R):
+        s = seed + i * 100
+        if mode == "tentacle":
+            fx = _simplex_noise_2d(H, W, frequency * 2, 2, s, t) * 2 - 1
+            fy = _simplex_noise_2d(H, W, frequency * 2, 2, s + 1000, t * 1.3) * 2 - 1
+            fy += np.sin(np.linspace(0, 1, H)[:, None] * np.pi * 3 + t) * 0.5
+        elif mode == "wave":
+            fx = np.sin(np.linspace(0, np.pi * frequency, H)[:, None] + t * 2) * np.ones((H, W))
+            fy = np.cos(np.linspace(0, np.pi * frequency, W)[None, :] + t * 1.5) * np.ones((H, W))
+        elif mode == "pulse":
+            yc, xc = np.arange(H)[:, None] - H // 2, np.arange(W)[None, :] - W // 2
+            r = np.sqrt(xc ** 2 + yc ** 2) + 1e-6
+            theta = np.arctan2(yc, xc)
+            pulse = np.sin(r * 0.05 - t * 3) * 0.5 + 0.5
+            fx, fy = np.cos(theta) * pulse, np.sin(theta) * pulse
+        else:
+            fx = _simplex_noise_2d(H, W, frequency, 2, s, t) * 2 - 1
+            fy = _simplex_noise_2d(H, W, frequency, 2, s + 1000, t * 1.3) * 2 - 1
+        md = max(H, W) * amplitude
+        fx, fy = fx * md, fy * md
+        yc = np.arange(H, dtype=np.float32)[:, None].repeat(W, axis=1)
+        xc = np.arange(W, dtype=np.float32)[None, :].repeat(H, axis=0)
+        w = cv2.remap(masks[i].numpy(), (xc + fx).astype(np.float32), (yc + fy).astype(np.float32), cv2.INTER_LINEAR, borderMode=cv2.BORDER_REFLECT)
+        warped.append(torch.from_numpy(w).view(1, 1, H, W))
+    msum = torch.zeros_like(warped[0])
+    for m in warped:
+        msum += m
+    gap = (msum < 0.1).float()
+    if gap.sum() > 0:
+        filled = list(warped)
+        for k in (5, 11, 21, 41):
+            filled = [m * (1 - gap) + F.max_pool2d(m, kernel_size=k, stride=1, padding=k // 2) * gap for m in filled]
+            msum = torch.zeros_like(filled[0])
+            for m in filled:
+                msum += m
+            gap = (msum < 0.1).float()
+            if gap.sum() == 0:
+                break
+        warped = filled
+    msum = msum.clamp(min=1e-6)
+    return torch.cat([(m / msum).view(1, H, W) for m in warped])
+
+
+# --------------------------------------------------------------------------- #
+# temporal: LAB EMA, motion-adaptive blend (SURVEY.md 8f N3)
+# --------------------------------------------------------------------------- #
+def lab_ema(frames_u8, smooth_lightness: bool, smooth_chroma: bool, smooth_alpha: float, chroma_alpha: float):
+    """pipeline.py:1938-1975 over a clip; numpy uint8 [N,H,W,3] -> same (Pillow's LAB transform, like the reference)."""
+    import numpy as np
+    from PIL import Image
+    pL = pa = pb = None
+    outs = []
+    for f in frames_u8:
+        lab_np = np.array(Image.fromarray(f, mode="RGB").convert("LAB"), dtype=np.uint8).astype(np.float32)
+        L, aC, bC = lab_np[..., 0], lab_np[..., 1], lab_np[..., 2]
+        if smooth_lightness:
+            if pL is None:
+                pL = L.copy()
+            pL = smooth_alpha * L + (1.0 - smooth_alpha) * pL
+            lab_np[..., 0] = np.clip(pL, 0, 255)
+        if smooth_chroma:
+            if pa is None:
+                pa, pb = aC.copy(), bC.copy()
+            pa = chroma_alpha * aC + (1.0 - chroma_alpha) * pa
+            pb = chroma_alpha * bC + (1.0 - chroma_alpha) * pb
+            lab_np[..., 1] = np.clip(pa, 0, 255)
+            lab_np[..., 2] = np.clip(pb, 0, 255)
+        outs.append(np.array(Image.fromarray(lab_np.astype(np.uint8), mode="LAB").convert("RGB")) if (smooth_lightness or smooth_chroma) else f)
+    return np.stack(outs)
+
+
+def motion_blend(styled_u8, original_u8, flow, blend: float, min_alpha: float = 0.40, motion_norm: float = 8.0, sigma: float = 3.0):
+    """pipeline.py:2072-2086 + the ToPILImage pack of :2094; numpy uint8 [H,W,3], flow fp32 [H,W,2] -> uint8 [H,W,3]."""
+    import cv2
+    import numpy as np
+    mag = np.sqrt(flow[..., 0] ** 2 + flow[..., 1] ** 2).astype(np.float32)
+    m = cv2.GaussianBlur(np.clip(mag / motion_norm, 0.0, 1.0), (0, 0), sigma)
+    alpha = float(blend) - (float(blend) - float(min_alpha)) * m
+    a3 = np.repeat(alpha[..., None], 3, axis=2)
+    s = torch.from_numpy(styled_u8).float().div(255).numpy()                     # ToTensor
+    o = torch.from_numpy(original_u8).float().div(255).numpy()
+    fused = (a3 * s + (1.0 - a3) * o).clip(0.0, 1.0).astype(np.float32)
+    return torch.from_numpy(fused).mul(255).byte().numpy()                        # ToPILImage

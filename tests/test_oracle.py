@@ -179,3 +179,42 @@ def test_u8_to_unit_shortcut_is_exact():
     assert int((q != exact).sum()) > 100
     q2 = fma(fma(-q, 255.0, k), r, q)
     assert np.array_equal(q2, exact)
+
+
+# ---- region masks / temporal post-processing: the restatements against the reference's own outputs -------------
+def test_mask_patterns_rotation_and_organic_warp_match_reference():
+    g = np.load(os.path.join(GOLDEN, "masks_patterns_60x84.npz"))
+    for key in g.files:
+        mode, c, s, f = key.split("_")
+        got = O.pattern_masks(60, 84, mode, int(c[1:]), int(s[1:]), int(f[1:])).numpy()
+        assert np.array_equal(got, g[key].astype(np.float32)), key
+    r = np.load(os.path.join(GOLDEN, "masks_rotate_60x84.npz"))
+    for key in r.files:
+        if key.startswith("rot_"):
+            assert np.array_equal(O.rotate_all_masks(torch.from_numpy(r["masks"]), float(key[4:])).numpy(), r[key]), key
+    o = np.load(os.path.join(GOLDEN, "masks_organic_60x84.npz"))
+    for mode in ("blob", "tentacle", "wave", "pulse"):
+        assert np.array_equal(O.warp_all_masks_organic(torch.from_numpy(o["masks"]), mode, 0.15, 3.0, 1.5, 42, 7).numpy(), o[f"{mode}_f7"]), mode
+    got = O.warp_all_masks_organic(torch.from_numpy(o["hard_masks"]).float(), "blob", 0.9, 5.0, 1.0, 5, 3).numpy()
+    assert np.array_equal(got, o["gappy_f3"]) and int(o["gaps_before_fill"]) > 0
+
+
+def test_lab_ema_and_motion_blend_match_reference():
+    g = np.load(os.path.join(GOLDEN, "lab_ema_48x64.npz"))
+    for tag, (sl, sc) in {"both": (True, True), "light": (True, False), "chroma": (False, True)}.items():
+        assert np.array_equal(O.lab_ema(g["frames"], sl, sc, float(g["smooth_alpha"]), float(g["chroma_alpha"])), g[f"out_{tag}"]), tag
+    m = np.load(os.path.join(GOLDEN, "motion_blend.npz"))
+    for t in ("54x70", "40x64"):
+        assert np.array_equal(O.motion_blend(m[f"styled_{t}"], m[f"orig_{t}"], m[f"flow_{t}"], float(m["blend"])), m[f"out_{t}"]), t
+
+
+def test_lab_tables_are_pillows_conversion():
+    """The 2^24-entry tables the LAB EMA kernel reads (temporal.lab_tables_host) against Pillow on random colours."""
+    from PIL import Image
+    from neuralstyletransferv1_b200.temporal import lab_tables_host
+    rgb2lab, lab2rgb = lab_tables_host()
+    px = np.random.default_rng(0).integers(0, 256, (64, 64, 3), dtype=np.uint8)
+    idx = (px[..., 0].astype(np.uint32) << 16) | (px[..., 1].astype(np.uint32) << 8) | px[..., 2]
+    unpack = lambda v: np.stack([v & 255, (v >> 8) & 255, (v >> 16) & 255], -1).astype(np.uint8)
+    assert np.array_equal(unpack(rgb2lab[idx]), np.array(Image.fromarray(px, mode="RGB").convert("LAB")))
+    assert np.array_equal(unpack(lab2rgb[idx]), np.array(Image.fromarray(px, mode="LAB").convert("RGB")))
