@@ -230,6 +230,20 @@ int nst_lab_ema_u8(const uint8_t* frames, uint8_t* out, int N, int H, int W, con
 int nst_motion_blend_u8(const uint8_t* styled, const uint8_t* original, const float* flow, uint8_t* out, float* scratch, int H, int W,
                         double blend, double min_alpha, double motion_norm, double sigma, void* stream);
 
+/* No counterpart in the reference: added for callers that cannot allocate device memory (code under
+ * CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).  Same computation and same results as nst_motion_blend_u8,
+ * but the H*W-float scratch plane is a file-scope `static __device__` array inside the library (csrc/temporal.cu) instead of a caller
+ * buffer: this call performs no cudaMalloc / cudaFree and calls no allocating routine.  Limits and rules:
+ *   - H * W <= NST_MOTION_STATIC_MAX_PIXELS (2^21 = 2 097 152 pixels: up to 1920x1088); larger frames return NST_ERR_INVALID -- use
+ *     nst_motion_blend_u8 with caller scratch.  Every GPU that loads the library holds the 8 MiB array until the process exits.
+ *   - the device must be current; the first call on each device resolves the array's device address (cudaGetSymbolAddress, cached, no
+ *     allocation) -- make that first call outside a graph capture.
+ *   - every call shares the one array per device and it keeps the last call's contents (each call overwrites all the entries it reads, so
+ *     nothing needs clearing): calls that overlap on the same GPU (different streams) race; serialise them or use nst_motion_blend_u8. */
+#define NST_MOTION_STATIC_MAX_PIXELS (1 << 21)
+int nst_motion_blend_u8_noalloc(const uint8_t* styled, const uint8_t* original, const float* flow, uint8_t* out, int H, int W,
+                                double blend, double min_alpha, double motion_norm, double sigma, void* stream);
+
 /* ---- introspection ------------------------------------------------------------------------- */
 
 /* Number of conv layers of the model, and per-layer facts of the last plan (after a forward or

@@ -109,3 +109,36 @@ extern "C" int nst_motion_blend_u8(const uint8_t* styled, const uint8_t* origina
   NST_CUDA_TRY(cudaGetLastError());
   return NST_OK;
 }
+
+// ---------------------------------------------------------------------------------------------
+// allocation-free variant of nst_motion_blend_u8 (no counterpart in the reference)
+// ---------------------------------------------------------------------------------------------
+// The row-filtered motion plane lives in a file-scope device array instead of caller scratch, for callers that cannot allocate
+// (CUDA graph capture, serving loops, harnesses that forbid cudaMalloc).  Every GPU that loads the library holds the array
+// (NST_MOTION_STATIC_MAX_PIXELS floats = 8 MiB) until the process exits.  `g_motion_rowf` is only a host-side stand-in in host code:
+// the device address is resolved once per device with cudaGetSymbolAddress and cached.
+namespace nst {
+constexpr int MOTION_STATIC_MAX_PIXELS = NST_MOTION_STATIC_MAX_PIXELS;
+static __device__ __align__(256) float g_motion_rowf[MOTION_STATIC_MAX_PIXELS];
+constexpr int MOTION_MAX_DEVICES = 64;
+static float* g_motion_rowf_addr[MOTION_MAX_DEVICES];       // device address of g_motion_rowf on each device, resolved on first use
+}  // namespace nst
+
+extern "C" int nst_motion_blend_u8_noalloc(const uint8_t* styled, const uint8_t* original, const float* flow, uint8_t* out, int H, int W,
+                                           double blend, double min_alpha, double motion_norm, double sigma, void* stream) {
+  if (H < 1 || W < 1) return api_fail(NST_ERR_INVALID, "motion_blend_noalloc: empty frame");
+  if ((long long)H * W > (long long)MOTION_STATIC_MAX_PIXELS)
+    return api_fail(NST_ERR_INVALID, "motion_blend_noalloc: %d x %d = %lld pixels exceed the static scratch of %d pixels; use nst_motion_blend_u8 with caller scratch",
+                    H, W, (long long)H * W, MOTION_STATIC_MAX_PIXELS);
+  int dev = -1;
+  NST_CUDA_TRY(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= MOTION_MAX_DEVICES) return api_fail(NST_ERR_INVALID, "motion_blend_noalloc: device ordinal %d out of range", dev);
+  float* rowf = __atomic_load_n(&g_motion_rowf_addr[dev], __ATOMIC_ACQUIRE);
+  if (rowf == nullptr) {                     // once per device, with that device current (two racing threads resolve the same address)
+    NST_CUDA_TRY(cudaGetSymbolAddress((void**)&rowf, g_motion_rowf));
+    if (rowf == nullptr) return api_fail(NST_ERR_CUDA, "motion_blend_noalloc: cudaGetSymbolAddress returned a null address");
+    __atomic_store_n(&g_motion_rowf_addr[dev], rowf, __ATOMIC_RELEASE);
+  }
+  // the row pass writes every one of the H*W entries the column pass reads: nothing in the array has to start at zero
+  return nst_motion_blend_u8(styled, original, flow, out, rowf, H, W, blend, min_alpha, motion_norm, sigma, stream);
+}

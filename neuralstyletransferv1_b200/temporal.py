@@ -114,3 +114,26 @@ def motion_blend(styled_u8: torch.Tensor, original_u8: torch.Tensor, flow: torch
                                      float(blend), float(min_alpha), float(motion_norm), float(sigma), torch.cuda.current_stream(styled_u8.device).cuda_stream)
     _lib.check(rc, "nst_motion_blend_u8")
     return out
+
+
+MOTION_STATIC_MAX_PIXELS = 1 << 21          # include/b200nst.h: NST_MOTION_STATIC_MAX_PIXELS
+
+
+def motion_blend_noalloc(styled_u8: torch.Tensor, original_u8: torch.Tensor, flow: torch.Tensor, out: torch.Tensor, blend: float,
+                         min_alpha: float = MIN_ALPHA, motion_norm: float = MOTION_NORM, sigma: float = GAUSS_SIGMA) -> torch.Tensor:
+    """``motion_blend`` without any allocation (no reference counterpart; added for callers under CUDA graph capture or in loops that may
+    not allocate): the scratch plane is a static array inside the library, ``out`` is the caller's buffer, inputs must already be
+    contiguous.  H * W <= MOTION_STATIC_MAX_PIXELS; calls that overlap on one GPU share that scratch and race."""
+    if not styled_u8.is_cuda:
+        raise RuntimeError("motion_blend_noalloc needs CUDA tensors; there is no CPU path")
+    H, W, _ = styled_u8.shape
+    for t, shp, dt, name in ((styled_u8, (H, W, 3), torch.uint8, "styled_u8"), (original_u8, (H, W, 3), torch.uint8, "original_u8"),
+                             (flow, (H, W, 2), torch.float32, "flow"), (out, (H, W, 3), torch.uint8, "out")):
+        if tuple(t.shape) != shp or t.dtype != dt or t.device != styled_u8.device or not t.is_contiguous():
+            raise ValueError(f"{name} must be a contiguous {dt} {shp} tensor on {styled_u8.device}")
+    lib = _lib.load()
+    with torch.cuda.device(styled_u8.device):
+        rc = lib.nst_motion_blend_u8_noalloc(styled_u8.data_ptr(), original_u8.data_ptr(), flow.data_ptr(), out.data_ptr(), H, W, float(blend),
+                                             float(min_alpha), float(motion_norm), float(sigma), torch.cuda.current_stream(styled_u8.device).cuda_stream)
+    _lib.check(rc, "nst_motion_blend_u8_noalloc")
+    return out
