@@ -213,6 +213,16 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, float (&v)[16]) {
   for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
 }
 
+// 16 consecutive accumulator columns, no wait: the caller overlaps the load with work on the previous fragment (tmem_ld_wait before use)
+__device__ __forceinline__ void tmem_ld16_nowait(uint32_t taddr, uint32_t (&r)[16]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+        "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+      : "r"(taddr)
+      : "memory");
+}
 // 32 consecutive accumulator columns of this thread's TMEM lane; the caller waits (tmem_ld_wait) before using them
 __device__ __forceinline__ void tmem_ld32_nowait(uint32_t taddr, uint32_t (&r)[32]) {
   asm volatile(
@@ -1323,6 +1333,96 @@ conv_tc_kernel(const __grid_constant__ TcArgs args) {
         mbar_wait_warp(ACC_FULL(buf), (it >> 1) & 1u, err, 5, wprof);
         tc_fence_after();
         const uint32_t tbase = tmem_base + ((uint32_t)(quad * 32) << 16) + buf * (uint32_t)(t.MB * t.NPAD);
+        if (p.out_fmt == OUT_F32_NHWC_STATS && !p.phase_mode && !(t.dbg & (4 | 65536))) {
+          // Plain layers, software-pipelined: the accumulator is drained as a flat sequence of (16-channel group, M block) fragments and
+          // the tcgen05.ld of fragment i + 1 is in flight while fragment i is packed, stored and added to the statistics (with four
+          // epilogue warps -- one per scheduler -- nothing else hides the TMEM latency; tcprof had this role 96 % busy on the first
+          // layer and the MMA warp 45 % of its time waiting for a free accumulator on the stride-2 32->64 layer).  The accumulator is
+          // released as soon as its last fragment is in registers.  Same per-lane summation order as the unpipelined form below.
+          const int MBn = t.MB;                                       // (small frames plan MB = 3, 5, ...: no shift / mask tricks)
+          const int nit = njc * MBn;
+          const int Wout = p.Wo;
+          const size_t plane_elems = (size_t)p.Ho * Wout * 8;
+          float s[16], q[16];
+#pragma unroll
+          for (int i = 0; i < 16; ++i) { s[i] = 0.f; q[i] = 0.f; }
+          int icg = 0, imb = 0, pcg = 0, pmb = 0;                     // (channel group, M block) of the next fragment to load / to process
+          auto issue = [&](uint32_t (&r)[16]) {
+            tmem_ld16_nowait(tbase + (uint32_t)(imb * t.NPAD + (icg << 4)), r);
+            if (++imb == MBn) { imb = 0; ++icg; }
+          };
+          auto release = [&]() { tc_fence_before(); mbar_arrive_warp(ACC_EMPTY(buf)); };
+          auto process = [&](const uint32_t (&r)[16]) {
+            const int mb = pmb, co0 = pcg << 4;
+            if (++pmb == MBn) { pmb = 0; ++pcg; }
+            const int m = mb * 128 + quad * 32 + lane;
+            const int ty = (int)(((float)m + 0.5f) * inv_p);
+            const int tx = m - ty * t.P;
+            const int oy = tc.ty0 + ty, ox = tc.tx0 + tx;
+            if (ty < t.TH && tx < t.TW && oy < p.Ho && ox < p.Wo) {
+              float v[16];
+#pragma unroll
+              for (int j = 0; j < 16; ++j) v[j] = __uint_as_float(r[j]);
+              const size_t plane0 = ((size_t)tc.n * (p.Cout >> 3) + (size_t)((p.co_off + co0) >> 3)) * plane_elems;
+              const size_t pix = (size_t)oy * Wout + (p.out_colsplit ? (ox & 1) * ((Wout + 1) >> 1) + (ox >> 1) : ox);
+              if (p.out16) {
+                __half* o = (__half*)p.out + plane0 + pix * 8;
+#pragma unroll
+                for (int hp = 0; hp < 2; ++hp)
+                  *reinterpret_cast<uint4*>(o + (size_t)hp * plane_elems) =
+                      make_uint4(pack2(v[8 * hp], v[8 * hp + 1], 0), pack2(v[8 * hp + 2], v[8 * hp + 3], 0),
+                                 pack2(v[8 * hp + 4], v[8 * hp + 5], 0), pack2(v[8 * hp + 6], v[8 * hp + 7], 0));
+              } else {
+                float* o = (float*)p.out + plane0 + pix * 8;
+#pragma unroll
+                for (int hp = 0; hp < 2; ++hp) {
+                  float4* o4 = reinterpret_cast<float4*>(o + (size_t)hp * plane_elems);
+                  o4[0] = make_float4(v[8 * hp], v[8 * hp + 1], v[8 * hp + 2], v[8 * hp + 3]);
+                  o4[1] = make_float4(v[8 * hp + 4], v[8 * hp + 5], v[8 * hp + 6], v[8 * hp + 7]);
+                }
+              }
+#pragma unroll
+              for (int j = 0; j < 16; ++j) { s[j] += v[j]; q[j] = fmaf(v[j], v[j], q[j]); }
+            }
+            if (mb == MBn - 1) {                    // last M block of this channel group: one butterfly over the 32 lanes
+#pragma unroll
+              for (int w = 8, off = 16; w >= 1; w >>= 1, off >>= 1) {
+                const bool up = (lane & off) != 0;
+#pragma unroll
+                for (int j = 0; j < w; ++j) {
+                  const float send_s = up ? s[j] : s[j + w];
+                  const float send_q = up ? q[j] : q[j + w];
+                  const float keep_s = up ? s[j + w] : s[j];
+                  const float keep_q = up ? q[j + w] : q[j];
+                  s[j] = keep_s + __shfl_xor_sync(0xffffffffu, send_s, off);
+                  q[j] = keep_q + __shfl_xor_sync(0xffffffffu, send_q, off);
+                }
+              }
+              const float ts = s[0] + __shfl_xor_sync(0xffffffffu, s[0], 1);
+              const float tq = q[0] + __shfl_xor_sync(0xffffffffu, q[0], 1);
+              if ((lane & 1) == 0) {
+                double2* w2 = reinterpret_cast<double2*>(wstat) + co0 + my_chan;
+                double2 cur = *w2;
+                cur.x += (double)ts; cur.y += (double)tq;
+                *w2 = cur;
+              }
+#pragma unroll
+              for (int j = 0; j < 16; ++j) { s[j] = 0.f; q[j] = 0.f; }
+            }
+          };
+          uint32_t ra[16], rb[16];
+          issue(ra);
+          for (int i = 0; i < nit; i += 2) {
+            tmem_ld_wait();
+            if (i + 1 < nit) issue(rb); else release();
+            process(ra);
+            if (i + 1 < nit) {
+              tmem_ld_wait();
+              if (i + 2 < nit) issue(ra); else release();
+              process(rb);
+            }
+          }
+        } else
         if (p.out_fmt == OUT_F32_NHWC_STATS) {
           const int nmb = (t.dbg & 4) ? 0 : t.MB;
           const int npair = p.phase_mode ? 2 : 1;                           // sub-pixel layers: column = phase*Cout + co, phase = a*2 + b;
