@@ -1,5 +1,6 @@
-"""Debug: the pipelined plain epilogue (default) must give bit-identical frames to the unpipelined one (NST_TC_DBG=65536): same
-per-lane summation order.  python tools/pipe_check.py  (spawns one process per setting)"""
+"""Debug: a re-scheduling of the same arithmetic must give bit-identical frames.  Default: the pipelined plain epilogue against the
+unpipelined one (NST_TC_DBG=65536: same per-lane summation order); `python tools/pipe_check.py NST_NO_RES_RING=1` compares any other
+knob (here: residual operand staged inside the operand stage instead of its own ring).  One process per setting."""
 import os, subprocess, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 CHILD = r'''
@@ -17,8 +18,12 @@ for arch, cls, preset in (("johnson", m.TransformerNet, "raw_255"), ("reconet", 
         print(arch, n, h, w, hashlib.md5(out.cpu().numpy().tobytes()).hexdigest(), bool(torch.equal(out, out2)), int(out.float().mean()))
 ''' % ROOT
 res = {}
+knob = sys.argv[1] if len(sys.argv) > 1 else "NST_TC_DBG=65536"
+kname, kval = knob.split("=")
 for dbg in ("0", "65536"):
-    env = dict(os.environ, NST_TC_DBG=dbg)
+    env = dict(os.environ)
+    if dbg != "0":
+        env[kname] = kval
     res[dbg] = subprocess.run([sys.executable, "-c", CHILD], env=env, capture_output=True, text=True)
     print("dbg", dbg); print(res[dbg].stdout); print(res[dbg].stderr[-600:])
 print("IDENTICAL" if res["0"].stdout == res["65536"].stdout and res["0"].stdout else "DIFFERENT")
