@@ -391,45 +391,94 @@ def feather_mask(mask: Tensor, feather_px: int) -> Tensor:
 
 def pattern_masks(H: int, W: int, mode: str, count: int, seed: int, feather: int) -> Tensor:
     """generate_region_masks for grid / diagonal / fractal / radial / waves / spiral / concentric (region_blend.py:109-172, 307-521,
-    925-981) as the reference's torch expressions; the random scalars come from the product's host helper `pattern_spec` (the same
-    `random.Random` draws -- pinned, like everything here, by the fixtures of tests/golden/make_golden_masks.py).  -> [count,H,W]."""
+    925-981) restated with the reference's torch expressions and its `random.Random` draw order (own restatement: nothing is shared with
+    the product's host helper; both are pinned by the fixtures of tests/golden/make_golden_masks.py).  -> [count,H,W]."""
     import math
     import random
-    from neuralstyletransferv1_b200.region_masks import pattern_spec
     rng = random.Random(seed)
     if mode == "random":
         mode = rng.choice(["grid", "diagonal", "voronoi", "fractal", "radial", "waves", "spiral", "concentric"])
-    sp = pattern_spec(H, W, mode, count, rng)
     yy = torch.arange(H, dtype=torch.float32).view(H, 1).expand(H, W)
     xx = torch.arange(W, dtype=torch.float32).view(1, W).expand(H, W)
-    hard = []
-    if mode in ("grid", "fractal"):
-        for (y1, y2, x1, x2) in sp.rects:
+
+    def bands(f):
+        return [((f >= i / count) & (f < (i + 1) / count)).float() for i in range(count)]
+
+    def boxes(rects):
+        out = []
+        for (y1, y2, x1, x2) in rects:
             m = torch.zeros(H, W)
             m[y1:y2, x1:x2] = 1.0
-            hard.append(m)
-    else:
-        if mode == "diagonal":
-            f = (xx + yy) if sp.p[0] else ((W - 1 - xx) + yy)
-            f = f / f.max()
-        elif mode == "radial":
-            f = (torch.atan2(yy - sp.p[1], xx - sp.p[0]) + math.pi + sp.p[2]) % (2 * math.pi)
-        elif mode == "waves":
-            yn, xn = yy / H, xx / W
-            t = (xn, yn, (xn + yn) / 2)[int(sp.p[2])]
-            pos = (yn, xn, t)[int(sp.p[2])] + torch.sin(t * sp.p[0] * 2 * math.pi + sp.p[3]) * sp.p[1]
-            f = (pos - pos.min()) / (pos.max() - pos.min() + 1e-6)
-        elif mode == "spiral":
-            yc, xc = yy - sp.p[1], xx - sp.p[0]
-            r = torch.sqrt(xc ** 2 + yc ** 2)
-            theta = torch.atan2(yc, xc) + math.pi + sp.p[3]
-            f = ((theta + r / max(H, W) * sp.p[2] * 2 * math.pi) % (2 * math.pi)) / (2 * math.pi)
-        elif mode == "concentric":
-            r = torch.sqrt((xx - sp.p[0]) ** 2 + (yy - sp.p[1]) ** 2)
-            f = r / r.max()
+            out.append(m)
+        return out
+
+    if mode == "grid":                                                    # :109-135
+        gs = int(math.ceil(math.sqrt(count)))
+        ch, cw = H / gs, W / gs
+        hard = boxes([(int((i // gs) * ch), min(int((i // gs + 1) * ch), H), int((i % gs) * cw), min(int((i % gs + 1) * cw), W)) for i in range(count)])
+    elif mode == "fractal":                                               # :307-364
+        regions = []
+
+        def subdivide(y1, y2, x1, x2, depth):
+            if len(regions) >= count:
+                return
+            if depth >= 4 or (y2 - y1) < 20 or (x2 - x1) < 20:
+                regions.append((y1, y2, x1, x2))
+                return
+            if rng.random() > 0.4 and depth > 0:
+                regions.append((y1, y2, x1, x2))
+                return
+            my = (y1 + y2) // 2 + rng.randint(-10, 10)
+            mx = (x1 + x2) // 2 + rng.randint(-10, 10)
+            my = max(y1 + 10, min(y2 - 10, my))
+            mx = max(x1 + 10, min(x2 - 10, mx))
+            quads = [(y1, my, x1, mx), (y1, my, mx, x2), (my, y2, x1, mx), (my, y2, mx, x2)]
+            rng.shuffle(quads)
+            for q in quads:
+                if len(regions) >= count:
+                    break
+                subdivide(*q, depth + 1)
+
+        subdivide(0, H, 0, W, 0)
+        hard = boxes(regions[:count])
+    elif mode == "diagonal":                                              # :138-171
+        f = (xx + yy) if rng.random() > 0.5 else ((W - 1 - xx) + yy)
+        hard = bands(f / f.max())
+    elif mode == "radial":                                                # :367-401
+        cx = W // 2 + rng.randint(-W // 4, W // 4)
+        cy = H // 2 + rng.randint(-H // 4, H // 4)
+        rotation = rng.random() * 2 * math.pi
+        ang = (torch.atan2(yy - cy, xx - cx) + math.pi + rotation) % (2 * math.pi)
+        wedge = 2 * math.pi / count
+        hard = [((ang >= i * wedge) & (ang < (i + 1) * wedge)).float() for i in range(count)]
+    elif mode == "waves":                                                 # :404-447
+        frequency = rng.uniform(1.5, 4.0)
+        amplitude = rng.uniform(0.05, 0.15)
+        direction = rng.choice(["horizontal", "vertical", "diagonal"])
+        phase = rng.random() * 2 * math.pi
+        yn, xn = yy / H, xx / W
+        if direction == "horizontal":
+            pos = yn + torch.sin(xn * frequency * 2 * math.pi + phase) * amplitude
+        elif direction == "vertical":
+            pos = xn + torch.sin(yn * frequency * 2 * math.pi + phase) * amplitude
         else:
-            raise ValueError(mode)
-        hard = [((f >= lo) & (f < hi)).float() for lo, hi in zip(sp.lo, sp.hi)]
+            d = (xn + yn) / 2
+            pos = d + torch.sin(d * frequency * 2 * math.pi + phase) * amplitude
+        hard = bands((pos - pos.min()) / (pos.max() - pos.min() + 1e-6))
+    elif mode == "spiral":                                                # :450-485
+        tightness = rng.uniform(2.0, 5.0)
+        rotation = rng.random() * 2 * math.pi
+        yc, xc = yy - H // 2, xx - W // 2
+        r = torch.sqrt(xc ** 2 + yc ** 2)
+        theta = torch.atan2(yc, xc) + math.pi + rotation
+        hard = bands(((theta + r / max(H, W) * tightness * 2 * math.pi) % (2 * math.pi)) / (2 * math.pi))
+    elif mode == "concentric":                                            # :488-521
+        cx = W // 2 + rng.randint(-W // 6, W // 6)
+        cy = H // 2 + rng.randint(-H // 6, H // 6)
+        r = torch.sqrt((xx - cx) ** 2 + (yy - cy) ** 2)
+        hard = bands(r / r.max())
+    else:
+        raise ValueError(mode)
     masks = [feather_mask(m.view(1, 1, H, W), feather) for m in hard]
     while len(masks) < count:
         masks.append(masks[-1].clone())
