@@ -221,6 +221,14 @@ int nst_lab_ema_u8(const uint8_t* frames, uint8_t* out, int N, int H, int W, con
                    float* prev_L, float* prev_a, float* prev_b, int init, int smooth_lightness, int smooth_chroma,
                    double smooth_alpha, double chroma_alpha, void* stream);
 
+/* Replaces: the blend stage of the per-frame loop on a frame that is already uint8 (after the LAB smoothing): `to_tensor(out_img)`
+ * (pipeline.py:1981), the mask composite (:2040-2043), the uniform blend that still applies after it (:2088-2092) and the ToPILImage pack
+ * (:2094), N frames per launch.  styled / original / out: [dev] uint8 [N,H,W,3]; mask: [dev] fp32 [N,H,W] or NULL; blend outside [0, 1)
+ * switches the uniform blend off; composite_mode 0 = keep (alpha * S + (1 - alpha) * O), 1 = replace.  Bit-exact (true /255, separately
+ * rounded multiplies and adds). */
+int nst_blend_pack_u8(const uint8_t* styled, const uint8_t* original, const float* mask, double blend, int composite_mode, uint8_t* out,
+                      int N, int H, int W, void* stream);
+
 /* Replaces: the motion-adaptive blend of pipeline.py:2072-2086 (MOTION_NORM / MIN_ALPHA / GAUSS_SIGMA of :1075-1077 are arguments):
  *   m = cv2.GaussianBlur(clip(|flow| / motion_norm, 0, 1), (0, 0), sigma);  alpha = blend - (blend - min_alpha) * m;
  *   out = trunc(clip(alpha * styled/255 + (1 - alpha) * original/255, 0, 1) * 255)

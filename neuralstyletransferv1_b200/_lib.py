@@ -56,6 +56,7 @@ PROTOTYPES = {
                                  C.c_int, C.c_int, C.c_int, C.c_double, C.c_double, C.c_void_p]),
     "nst_motion_blend_u8": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_double, C.c_double,
                                       C.c_double, C.c_double, C.c_void_p]),
+    "nst_blend_pack_u8": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_double, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p]),
     "nst_motion_blend_u8_noalloc": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_double, C.c_double,
                                               C.c_double, C.c_double, C.c_void_p]),
     "nst_composite_regions_u8": (C.c_int, [C.POINTER(C.c_void_p), C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int,

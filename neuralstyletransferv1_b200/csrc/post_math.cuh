@@ -259,6 +259,23 @@ PM_HD void motion_fuse(float m, float max_alpha, float alpha_span, const uint8_t
   }
 }
 
+// mask composite (pipeline.py:2040-2043), then the uniform blend that still applies after it (:2088-2092), then the ToPILImage pack
+// (:2094), for one channel of a frame that is already uint8 (`to_tensor(out_img)`, :1981): blend outside [0, 1) = off
+PM_HD uint8_t blend_pack_u8(uint8_t styled, uint8_t original, bool has_mask, float a, int composite_mode, float blend, float blend_comp) {
+  float o01 = unit255((float)styled);
+  const float og = unit255((float)original);
+  if (has_mask) {
+    const float na = sub(1.0f, a);
+    o01 = composite_mode == 0 ? add(mul(a, o01), mul(na, og)) : add(mul(na, o01), mul(a, og));
+    o01 = fminf(fmaxf(o01, 0.f), 1.f);
+  }
+  if (blend >= 0.f && blend < 1.f) {
+    o01 = add(mul(blend, o01), mul(blend_comp, og));
+    o01 = fminf(fmaxf(o01, 0.f), 1.f);
+  }
+  return (uint8_t)mul(o01, 255.f);
+}
+
 // ---------------------------------------------------------------------------------------------
 // LAB EMA (pipeline.py:1938-1975): one frame of one pixel; tables map (c0 << 16 | c1 << 8 | c2) -> c0' | c1' << 8 | c2' << 16
 // ---------------------------------------------------------------------------------------------

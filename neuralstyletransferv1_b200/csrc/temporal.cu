@@ -71,6 +71,16 @@ __global__ void __launch_bounds__(256) motion_col_blend_kernel(const __grid_cons
   }
 }
 
+struct BlendPackArgs { const uint8_t* styled; const uint8_t* original; const float* mask; uint8_t* out; size_t npix; int composite_mode; float blend, blend_comp; };
+__global__ void __launch_bounds__(256) blend_pack_kernel(const __grid_constant__ BlendPackArgs a) {
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < a.npix; i += (size_t)gridDim.x * blockDim.x) {
+    const float al = a.mask ? a.mask[i] : 0.f;
+#pragma unroll
+    for (int c = 0; c < 3; ++c)
+      a.out[i * 3 + c] = blend_pack_u8(a.styled[i * 3 + c], a.original[i * 3 + c], a.mask != nullptr, al, a.composite_mode, a.blend, a.blend_comp);
+  }
+}
+
 static inline int grid_for(int hw) { return std::min((hw + 255) / 256, 148 * 16); }
 
 }  // namespace nst
@@ -88,6 +98,18 @@ extern "C" int nst_lab_ema_u8(const uint8_t* frames, uint8_t* out, int N, int H,
   a.aL = (float)smooth_alpha; a.aL_comp = (float)(1.0 - smooth_alpha);
   a.aC = (float)chroma_alpha; a.aC_comp = (float)(1.0 - chroma_alpha);
   lab_ema_kernel<<<grid_for(H * W), 256, 0, (cudaStream_t)stream>>>(a);
+  NST_CUDA_TRY(cudaGetLastError());
+  return NST_OK;
+}
+
+extern "C" int nst_blend_pack_u8(const uint8_t* styled, const uint8_t* original, const float* mask, double blend, int composite_mode, uint8_t* out,
+                                 int N, int H, int W, void* stream) {
+  if (!styled || !original || !out || N < 1 || H < 1 || W < 1) return api_fail(NST_ERR_INVALID, "blend_pack: null / empty argument");
+  BlendPackArgs a;
+  a.styled = styled; a.original = original; a.mask = mask; a.out = out; a.npix = (size_t)N * H * W; a.composite_mode = composite_mode;
+  const bool on = blend >= 0.0 && blend < 1.0;
+  a.blend = on ? (float)blend : 2.f; a.blend_comp = (float)(1.0 - blend);       // Python computes 1.0 - blend in double before torch narrows it
+  blend_pack_kernel<<<(int)std::min<size_t>((a.npix + 255) / 256, (size_t)148 * 16), 256, 0, (cudaStream_t)stream>>>(a);
   NST_CUDA_TRY(cudaGetLastError());
   return NST_OK;
 }

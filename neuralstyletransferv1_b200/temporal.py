@@ -116,6 +116,28 @@ def motion_blend(styled_u8: torch.Tensor, original_u8: torch.Tensor, flow: torch
     return out
 
 
+def blend_pack(styled_u8: torch.Tensor, original_u8: torch.Tensor, blend: float = 1.0, mask: Optional[torch.Tensor] = None,
+               composite_mode: str = "keep") -> torch.Tensor:
+    """Mask composite, then uniform blend, then pack, of frames that are already uint8 (pipeline.py:1981, 2040-2043, 2088-2094).
+    styled_u8 / original_u8: uint8 [N, H, W, 3] CUDA; mask: fp32 [N, H, W] or None."""
+    if not styled_u8.is_cuda:
+        raise RuntimeError("blend_pack needs CUDA tensors; there is no CPU path")
+    N, H, W, _ = styled_u8.shape
+    if tuple(original_u8.shape) != (N, H, W, 3) or styled_u8.dtype != torch.uint8 or original_u8.dtype != torch.uint8:
+        raise ValueError("styled_u8 and original_u8 must be uint8 [N, H, W, 3]")
+    if mask is not None and (tuple(mask.shape) != (N, H, W) or mask.dtype != torch.float32):
+        raise ValueError("mask must be float32 [N, H, W]")
+    lib = _lib.load()
+    styled_u8, original_u8 = styled_u8.contiguous(), original_u8.contiguous()
+    m = mask.contiguous() if mask is not None else None
+    out = torch.empty_like(styled_u8)
+    with torch.cuda.device(styled_u8.device):
+        rc = lib.nst_blend_pack_u8(styled_u8.data_ptr(), original_u8.data_ptr(), m.data_ptr() if m is not None else None, float(blend),
+                                   _lib.COMPOSITE_MODE[composite_mode], out.data_ptr(), N, H, W, torch.cuda.current_stream(styled_u8.device).cuda_stream)
+    _lib.check(rc, "nst_blend_pack_u8")
+    return out
+
+
 MOTION_STATIC_MAX_PIXELS = 1 << 21          # include/b200nst.h: NST_MOTION_STATIC_MAX_PIXELS
 
 

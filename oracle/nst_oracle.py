@@ -611,3 +611,34 @@ def motion_blend(styled_u8, original_u8, flow, blend: float, min_alpha: float = 
     o = torch.from_numpy(original_u8).float().div(255).numpy()
     fused = (a3 * s + (1.0 - a3) * o).clip(0.0, 1.0).astype(np.float32)
     return torch.from_numpy(fused).mul(255).byte().numpy()                        # ToPILImage
+
+
+def post_chain(out01_seq, orig_u8_seq, flows, masks=None, flow_ema_on=False, flow_alpha=0.85, smooth_lightness=False, smooth_chroma=False,
+               smooth_alpha=0.7, chroma_alpha=0.85, blend=1.0, motion_blend_on=False, composite_mode="keep"):
+    """The tail of the reference's per-frame loop over a clip (pipeline.py:1884-2094), composed from the restatements above:
+    flow EMA -> pack -> LAB EMA -> mask composite / motion-adaptive or uniform blend -> pack.  out01_seq: torch fp32 [N,3,H,W] (clamped);
+    orig_u8_seq: numpy uint8 [N,H,W,3]; flows: list of numpy [H,W,2] or None; masks: numpy [N,H,W] or None.  -> numpy uint8 [N,H,W,3]."""
+    import numpy as np
+    N = len(out01_seq)
+    prev = None
+    fused, last_flow = [], []
+    for i in range(N):
+        cur = out01_seq[i].permute(1, 2, 0).numpy().astype(np.float32)
+        lf = None
+        if flow_ema_on and flows[i] is not None and prev is not None:
+            cur = flow_ema(cur, prev, flows[i], flow_alpha)
+            lf = flows[i]
+        prev = cur
+        fused.append(pack_u8(torch.from_numpy(cur).permute(2, 0, 1)[None])[0].numpy())
+        last_flow.append(lf)
+    smooth = lab_ema(np.stack(fused), smooth_lightness, smooth_chroma, smooth_alpha, chroma_alpha)
+    outs = []
+    for i in range(N):
+        if motion_blend_on and last_flow[i] is not None and masks is None:
+            outs.append(motion_blend(smooth[i], orig_u8_seq[i], last_flow[i], blend))
+            continue
+        s01 = torch.from_numpy(smooth[i]).permute(2, 0, 1).float().div(255)[None]
+        x01 = torch.from_numpy(orig_u8_seq[i]).permute(2, 0, 1).float().div(255)[None]
+        m = torch.from_numpy(masks[i])[None] if masks is not None else None
+        outs.append(post_u8(s01, x01, blend, m, composite_mode)[0].numpy())
+    return np.stack(outs)

@@ -134,3 +134,46 @@ def test_motion_blend_is_opencvs_bit_for_bit():
     flow = torch.randn(1080, 1920, 2, generator=torch.Generator().manual_seed(1)) * 5
     got = m.motion_blend(s[0].cuda(), s[1].cuda(), flow.cuda(), 0.85)
     assert np.array_equal(got.cpu().numpy(), O.motion_blend(s[0].numpy(), s[1].numpy(), flow.numpy(), 0.85))
+
+
+# ---- the whole per-frame tail (post_chain.PostChain) against the literal reference loop ------------------------------------------------
+@pytest.mark.parametrize("name", ["ema_lab_blend", "ema_motion", "mask_light", "plain"])
+def test_post_chain_matches_the_reference_loop_bit_for_bit(name):
+    import neuralstyletransferv1_b200 as m
+    from test_oracle import CHAIN_CONFIGS, load_chain_fixture
+    g, out01, orig, flows, masks = load_chain_fixture()
+    c = CHAIN_CONFIGS[name]
+    mk = lambda: m.PostChain(flow_ema=c["flow_ema_on"], flow_alpha=c["flow_alpha"], smooth_lightness=c["smooth_lightness"],
+                             smooth_chroma=c["smooth_chroma"], smooth_alpha=c["smooth_alpha"], chroma_alpha=c["chroma_alpha"], blend=c["blend"],
+                             motion_blend=c["motion_blend_on"], composite_mode=c["composite_mode"])
+    dflows = [torch.from_numpy(f).cuda() if f is not None else None for f in flows]
+    dmasks = torch.from_numpy(masks).cuda() if name == "mask_light" else None
+    chain = mk()
+    got = chain(out01.cuda(), torch.from_numpy(orig).cuda(), dflows, dmasks).cpu().numpy()
+    assert np.array_equal(got, g["out_" + name]), name
+    chain = mk()                                           # the state carries across calls: 2 + 3 frames == 5 frames
+    parts = [chain(out01[a:b].cuda(), torch.from_numpy(orig[a:b]).cuda(), dflows[a:b], dmasks[a:b] if dmasks is not None else None)
+             for a, b in ((0, 2), (2, 5))]
+    assert np.array_equal(torch.cat(parts).cpu().numpy(), g["out_" + name]), name
+
+
+def test_post_chain_at_1080p_behind_the_generator():
+    """Generator -> fp32 out01 -> PostChain for a 3-frame 1080p clip: bit-identical to the oracle's chain applied to the SAME device out01
+    (the tail is byte work), and the frames stay within the network tolerance of the all-CPU path."""
+    import neuralstyletransferv1_b200 as m
+    model = m.TransformerNet().to("cuda:0")
+    sd = synth.make_state_dict("johnson", 0)
+    model.load_state_dict(sd)
+    model.eval()
+    frames = synth.synthetic_frames_u8(3, 1080, 1920, seed=9)
+    x = frames.permute(0, 3, 1, 2).float().cuda()                       # raw_255 input (pipeline.py:1473)
+    with torch.no_grad():
+        out01 = (model(x) / 255.0).clamp(0, 1)
+    gen = torch.Generator().manual_seed(3)
+    flows = [None] + [torch.randn(1080, 1920, 2, generator=gen) * 3 for _ in range(2)]
+    cfg = dict(flow_alpha=0.8, smooth_lightness=True, smooth_chroma=True, smooth_alpha=0.7, chroma_alpha=0.85, blend=0.9)
+    chain = m.PostChain(flow_ema=True, motion_blend=True, **cfg)
+    got = chain(out01, frames.cuda(), [f.cuda() if f is not None else None for f in flows]).cpu().numpy()
+    want = O.post_chain(out01.cpu(), frames.numpy(), [f.numpy() if f is not None else None for f in flows], None, flow_ema_on=True,
+                        motion_blend_on=True, **cfg)
+    assert np.array_equal(got, want)

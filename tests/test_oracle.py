@@ -218,3 +218,32 @@ def test_lab_tables_are_pillows_conversion():
     unpack = lambda v: np.stack([v & 255, (v >> 8) & 255, (v >> 16) & 255], -1).astype(np.uint8)
     assert np.array_equal(unpack(rgb2lab[idx]), np.array(Image.fromarray(px, mode="RGB").convert("LAB")))
     assert np.array_equal(unpack(lab2rgb[idx]), np.array(Image.fromarray(px, mode="LAB").convert("RGB")))
+
+
+CHAIN_CONFIGS = {      # tests/golden/make_golden_chain.py: CONFIGS
+    "ema_lab_blend": dict(flow_ema_on=True, flow_alpha=0.7, smooth_lightness=True, smooth_chroma=True, smooth_alpha=0.7, chroma_alpha=0.85,
+                          blend=0.8, motion_blend_on=False, composite_mode="keep"),
+    "ema_motion": dict(flow_ema_on=True, flow_alpha=0.85, smooth_lightness=False, smooth_chroma=False, smooth_alpha=0.7, chroma_alpha=0.85,
+                       blend=0.9, motion_blend_on=True, composite_mode="keep"),
+    "mask_light": dict(flow_ema_on=True, flow_alpha=0.6, smooth_lightness=True, smooth_chroma=False, smooth_alpha=0.5, chroma_alpha=0.85,
+                       blend=0.75, motion_blend_on=True, composite_mode="replace"),
+    "plain": dict(flow_ema_on=False, flow_alpha=0.7, smooth_lightness=False, smooth_chroma=False, smooth_alpha=0.7, chroma_alpha=0.85,
+                  blend=1.0, motion_blend_on=False, composite_mode="keep"),
+}
+
+
+def load_chain_fixture():
+    g = np.load(os.path.join(GOLDEN, "post_chain_48x72.npz"))
+    out01 = torch.from_numpy(g["out01_q4096"].astype(np.float32) / 4096.0)
+    flows = [g["flows"][i].astype(np.float32) if g["has_flow"][i] else None for i in range(len(out01))]
+    masks = g["masks_q1024"].astype(np.float32) / 1024.0
+    return g, out01, g["orig"], flows, masks
+
+
+@pytest.mark.parametrize("name", sorted(CHAIN_CONFIGS))
+def test_post_chain_matches_the_reference_loop(name):
+    """The loop tail restated from its parts (flow EMA, pack, LAB EMA, composite / blends) against the literal loop of
+    pipeline.py:1884-2094 run over a 5-frame clip (one frame without a flow estimate)."""
+    g, out01, orig, flows, masks = load_chain_fixture()
+    got = O.post_chain(out01, orig, flows, masks if name == "mask_light" else None, **CHAIN_CONFIGS[name])
+    assert np.array_equal(got, g["out_" + name]), name
