@@ -200,6 +200,13 @@ int nst_rotate_masks_f32(const float* masks, float* out, int R, int H, int W, do
 int nst_warp_masks_organic_f32(const float* masks, float* out, int R, int H, int W, int mode, double amplitude, double frequency,
                                double time_offset, const double* offsets, float* scratch, void* stream);
 
+/* Replaces: the reduction of region_blend.compute_mask_bbox (region_blend.py:1969-1994), the first step of prepare_region_crops (:2019-2059),
+ * for R masks at once: boxes_dev[4r..4r+3] = (min x, min y, max x, max y) over the pixels with mask > threshold (compared in double, like numpy's
+ * fp32 array against the Python float 0.01), or
+ * (INT_MAX, INT_MAX, -1, -1) for an empty mask (the caller then takes the full frame, like the reference).  masks: [dev] fp32 [R,H,W];
+ * boxes_dev: [dev] 4*R ints.  The host adds +1 to the maxima and the padding (neuralstyletransferv1_b200/region_crops.py). */
+int nst_mask_bboxes(const float* masks, int R, int H, int W, double threshold, int* boxes_dev, void* stream);
+
 /* Scratch (in floats) the two mask calls above need. */
 size_t nst_mask_scratch_floats(int R, int H, int W);
 

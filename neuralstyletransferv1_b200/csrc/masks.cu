@@ -12,6 +12,7 @@
 //                                   gap counter is zero (no host round trip)
 //   normalize_masks                 m / clamp(sum, 1e-6)
 #include <algorithm>
+#include <climits>
 #include <cmath>
 #include <cstring>
 
@@ -223,6 +224,34 @@ __global__ void __launch_bounds__(256) normalize_masks_kernel(const float* in, f
   }
 }
 
+// ---------------------------------------------------------------------------------------------
+// tight bounding boxes (region_blend.compute_mask_bbox, region_blend.py:1969-1994)
+// ---------------------------------------------------------------------------------------------
+// box[4r .. 4r+3] = (min x, min y, max x, max y) over the pixels of mask r above the threshold; one atomic quartet per block and region
+__global__ void mask_bbox_init_kernel(int* box, int R) {
+  const int r = blockIdx.x * blockDim.x + threadIdx.x;
+  if (r < R) { box[4 * r] = INT_MAX; box[4 * r + 1] = INT_MAX; box[4 * r + 2] = -1; box[4 * r + 3] = -1; }
+}
+__global__ void __launch_bounds__(256) mask_bbox_kernel(const float* masks, int* box, int H, int W, double threshold) {
+  const int hw = H * W, r = blockIdx.y;
+  const float* pl = masks + (size_t)r * hw;
+  int x0 = INT_MAX, y0 = INT_MAX, x1 = -1, y1 = -1;
+  for (int pix = blockIdx.x * blockDim.x + threadIdx.x; pix < hw; pix += gridDim.x * blockDim.x) {
+    if ((double)pl[pix] > threshold) {                  // numpy: fp32 array > Python double
+      const int y = pix / W, x = pix - y * W;
+      x0 = min(x0, x); y0 = min(y0, y); x1 = max(x1, x); y1 = max(y1, y);
+    }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    x0 = min(x0, __shfl_xor_sync(0xffffffffu, x0, o)); y0 = min(y0, __shfl_xor_sync(0xffffffffu, y0, o));
+    x1 = max(x1, __shfl_xor_sync(0xffffffffu, x1, o)); y1 = max(y1, __shfl_xor_sync(0xffffffffu, y1, o));
+  }
+  if ((threadIdx.x & 31) == 0 && x1 >= 0) {
+    atomicMin(box + 4 * r, x0); atomicMin(box + 4 * r + 1, y0); atomicMax(box + 4 * r + 2, x1); atomicMax(box + 4 * r + 3, y1);
+  }
+}
+
 static inline int grid_for(int hw) { return std::min((hw + 255) / 256, 148 * 16); }
 
 }  // namespace nst
@@ -313,4 +342,13 @@ extern "C" size_t nst_mask_scratch_floats(int R, int H, int W) {
   const size_t pattern = 4 + hw + (hw + 3) / 4 + (size_t)R * hw;
   const size_t organic = 4 * PAT_MAX_R + 8 + 3 * (size_t)R * hw + (hw + 3) / 4;
   return std::max(pattern, organic);
+}
+
+extern "C" int nst_mask_bboxes(const float* masks, int R, int H, int W, double threshold, int* boxes_dev, void* stream) {
+  if (!masks || !boxes_dev || R < 1 || H < 1 || W < 1) return api_fail(NST_ERR_INVALID, "mask_bboxes: null / empty argument");
+  cudaStream_t st = (cudaStream_t)stream;
+  mask_bbox_init_kernel<<<(R + 63) / 64, 64, 0, st>>>(boxes_dev, R);
+  mask_bbox_kernel<<<dim3(std::min((H * W + 255) / 256, 148 * 4), R), 256, 0, st>>>(masks, boxes_dev, H, W, threshold);
+  NST_CUDA_TRY(cudaGetLastError());
+  return NST_OK;
 }

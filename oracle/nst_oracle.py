@@ -642,3 +642,57 @@ def post_chain(out01_seq, orig_u8_seq, flows, masks=None, flow_ema_on=False, flo
         m = torch.from_numpy(masks[i])[None] if masks is not None else None
         outs.append(post_u8(s01, x01, blend, m, composite_mode)[0].numpy())
     return np.stack(outs)
+
+
+# --------------------------------------------------------------------------- #
+# crop-based region styling
+# --------------------------------------------------------------------------- #
+def prepare_region_crops(masks: Tensor, configs, H: int, W: int, padding: int = 64):
+    """region_blend.compute_mask_bbox / pad_bbox / prepare_region_crops (region_blend.py:1969-2059).  masks [R,H,W]; configs: dicts with
+    model_indices, model_weights, scale.  -> the crop dicts composite_from_crops above takes (+ bbox, scale)."""
+    import numpy as np
+    crops = []
+    for idx, cfg in enumerate(configs):
+        m2 = masks[idx].numpy()
+        rows, cols = np.any(m2 > 0.01, axis=1), np.any(m2 > 0.01, axis=0)
+        if not np.any(rows) or not np.any(cols):
+            bbox = (0, 0, W, H)
+        else:
+            y1, y2 = np.where(rows)[0][[0, -1]]
+            x1, x2 = np.where(cols)[0][[0, -1]]
+            bbox = (int(x1), int(y1), int(x2) + 1, int(y2) + 1)
+        pb = (max(0, bbox[0] - padding), max(0, bbox[1] - padding), min(W, bbox[2] + padding), min(H, bbox[3] + padding))
+        crops.append(dict(region_idx=idx, bbox=bbox, padded_bbox=pb, crop_mask=masks[idx][None, None, pb[1]:pb[3], pb[0]:pb[2]].clone(),
+                          model_indices=list(cfg["model_indices"]), model_weights=list(cfg["model_weights"]), scale=float(cfg["scale"])))
+    return crops
+
+
+def region_crop_style(frame_u8: Tensor, masks: Tensor, configs, archs, sds, presets, padding: int = 64, use_original: bool = True) -> Tensor:
+    """The `--region_optimize` branch of the loop (pipeline.py:1293-1400) for Transformer / ReCoNet models: style the padded box of every
+    region with the models it uses, composite.  frame_u8 [H,W,3]; -> out01 fp32 [3,H,W]."""
+    H, W, _ = frame_u8.shape
+    x01 = frame_u8.permute(2, 0, 1).float() / 255.0
+    crops = prepare_region_crops(masks, configs, H, W, padding)
+    mean = torch.tensor(IMAGENET_MEAN).view(1, 3, 1, 1)
+    std = torch.tensor(IMAGENET_STD).view(1, 3, 1, 1)
+    styled = {}
+    for mi in sorted({m for c in crops for m in c["model_indices"] if m >= 0}):
+        styled[mi] = {}
+        for c in crops:
+            if mi not in c["model_indices"]:
+                continue
+            x1, y1, x2, y2 = c["padded_bbox"]
+            ch, cw = y2 - y1, x2 - x1
+            crop = x01[:, y1:y2, x1:x2].clone().unsqueeze(0)
+            if c["scale"] < 1.0:
+                crop = F.interpolate(crop, size=(max(1, int(ch * c["scale"])), max(1, int(cw * c["scale"]))), mode="bilinear", align_corners=False)
+            if presets[mi] == "imagenet_255":
+                out = (forward(archs[mi], sds[mi], (crop * 255.0 - mean * 255.0) / (std * 255.0)) / 255.0).clamp(0, 1)
+            elif presets[mi] == "imagenet_01":
+                out = (forward(archs[mi], sds[mi], (crop - mean) / std) * std + mean).clamp(0, 1)
+            else:
+                out = (forward(archs[mi], sds[mi], crop * 255.0) / 255.0).clamp(0, 1)
+            if c["scale"] < 1.0:
+                out = F.interpolate(out, size=(ch, cw), mode="bilinear", align_corners=False)
+            styled[mi][c["region_idx"]] = out.squeeze(0)
+    return composite_from_crops(styled, crops, x01 if use_original else None, H, W)

@@ -246,3 +246,46 @@ def test_composite_batch_vector_path_is_bit_exact(mask_dtype):
     for n in range(N):
         want = O.composite_regions_advanced([f(s[n]) for s in srcs], [mk[None, None] for mk in mf], idx, wts, f(orig[n]))
         assert torch.equal(got[n], O.pack_u8(want[None])[0]), n
+
+
+def test_region_crops_bboxes_and_crop_styling():
+    """SURVEY 8f N4.  (1) prepare_region_crops on the device against the reference's boxes (tight box of mask > 0.01, padding, the
+    full-frame box of an empty mask, values just either side of the threshold).  (2) RegionCropStyler -- crop, optional down-scale,
+    preset, generator, post, composite_from_crops -- against the all-CPU oracle of pipeline.py:1293-1400: the frame goes through two
+    generators, so the bar is the network tolerance (max |d| <= 2 on the uint8 pack, PSNR >= 45 dB)."""
+    import neuralstyletransferv1_b200 as m
+    from oracle import nst_oracle as O
+    g = np.load(os.path.join(GOLDEN, "region_crops_96x128.npz"))
+    masks = torch.from_numpy(g["masks"]).cuda()
+    cfgs = [m.RegionConfig([0], [1.0], 1.0) for _ in range(masks.shape[0])]
+    for pad in (12, 64):
+        crops = m.prepare_region_crops(masks, cfgs, 96, 128, padding=pad)
+        assert [list(c.bbox) for c in crops] == g[f"bbox_p{pad}"].tolist()
+        assert [list(c.padded_bbox) for c in crops] == g[f"padded_p{pad}"].tolist()
+        for c in crops:
+            x1, y1, x2, y2 = c.padded_bbox
+            assert torch.equal(c.crop_mask, masks[c.region_idx, y1:y2, x1:x2])
+
+    H, W = 180, 240
+    rmasks = m.generate_region_masks(H, W, "voronoi", 3, seed=5, feather=5)
+    rmasks = rmasks * (torch.arange(W, device="cuda").view(1, 1, W) < W - 40)            # a strip no region covers: gap fill by the original
+    cfgs = [m.RegionConfig([0], [1.0], 1.0), m.RegionConfig([1, -1], [0.6, 0.4], 1.0), m.RegionConfig([0, 1], [0.5, 0.5], 0.5)]
+    sds = [synth.make_state_dict("johnson", 0), synth.make_state_dict("johnson", 1)]
+    models = []
+    for sd in sds:
+        mod = m.TransformerNet().to("cuda:0")
+        mod.load_state_dict(sd)
+        mod.eval()
+        models.append(mod)
+    presets = ["raw_255", "imagenet_255"]
+    frame = synth.synthetic_frames_u8(1, H, W, seed=17)[0]
+    styler = m.RegionCropStyler(models, presets, rmasks, cfgs, padding=12, use_original=True)
+    got01 = styler(frame.cuda()).cpu()
+    ocfgs = [dict(model_indices=c.model_indices, model_weights=c.model_weights, scale=c.scale) for c in cfgs]
+    want01 = O.region_crop_style(frame, rmasks.cpu(), ocfgs, ["johnson", "johnson"], sds, presets, padding=12, use_original=True)
+    assert got01.shape == want01.shape == (3, H, W)
+    mx, psnr = O.u8_metrics(O.pack_u8(got01[None]), O.pack_u8(want01[None]))
+    assert mx <= 2 and psnr >= 45.0, (mx, psnr)
+    strip = (rmasks.sum(0) < 0.1).cpu()                                               # the uncovered strip is the original, exactly
+    x01 = frame.permute(2, 0, 1).float() / 255.0
+    assert strip.any() and torch.equal(got01[:, strip], x01[:, strip])

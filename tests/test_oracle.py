@@ -247,3 +247,13 @@ def test_post_chain_matches_the_reference_loop(name):
     g, out01, orig, flows, masks = load_chain_fixture()
     got = O.post_chain(out01, orig, flows, masks if name == "mask_light" else None, **CHAIN_CONFIGS[name])
     assert np.array_equal(got, g["out_" + name]), name
+
+
+def test_prepare_region_crops_matches_reference():
+    g = np.load(os.path.join(GOLDEN, "region_crops_96x128.npz"))
+    masks = torch.from_numpy(g["masks"])
+    cfgs = [dict(model_indices=[0], model_weights=[1.0], scale=1.0)] * masks.shape[0]
+    for pad in (12, 64):
+        crops = O.prepare_region_crops(masks, cfgs, 96, 128, padding=pad)
+        assert [list(c["bbox"]) for c in crops] == g[f"bbox_p{pad}"].tolist()
+        assert [list(c["padded_bbox"]) for c in crops] == g[f"padded_p{pad}"].tolist()
