@@ -12,6 +12,7 @@ from .region_masks import (MorphAnimation, generate_region_masks, rotate_all_mas
                            warp_all_masks_organic)
 from .temporal import LabEma, motion_blend  # noqa: F401
 from .post_chain import PostChain  # noqa: F401
+from .region_anim import BlendAnimation, ScaleAnimation, animated_scale, animated_weights, harmonic_value  # noqa: F401
 from .region_crops import RegionConfig, RegionCrop, RegionCropStyler, mask_bboxes, prepare_region_crops  # noqa: F401
 from .modules import ReCoNet, TransformerNet, TransformerNetNST  # noqa: F401
 from .reconet_model import ReCoNetModel  # noqa: F401
@@ -19,5 +20,5 @@ from .sharding import shard_range, shard_sizes  # noqa: F401
 
 __all__ = ["Engine", "composite_regions", "composite_regions_batch", "composite_from_crops", "flow_ema", "FramePipeline",
            "MultiGpuFramePipeline", "voronoi_masks", "generate_region_masks", "rotate_all_masks", "warp_all_masks_organic",
-           "MorphAnimation", "LabEma", "motion_blend", "PostChain", "RegionConfig", "RegionCrop", "RegionCropStyler", "mask_bboxes", "prepare_region_crops", "io_preset_affine", "TransformerNet", "TransformerNetNST",
+           "MorphAnimation", "LabEma", "motion_blend", "PostChain", "BlendAnimation", "ScaleAnimation", "animated_scale", "animated_weights", "harmonic_value", "RegionConfig", "RegionCrop", "RegionCropStyler", "mask_bboxes", "prepare_region_crops", "io_preset_affine", "TransformerNet", "TransformerNetNST",
            "ReCoNet", "ReCoNetModel", "shard_range", "shard_sizes"]

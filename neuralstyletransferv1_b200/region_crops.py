@@ -19,6 +19,7 @@ import torch
 import torch.nn.functional as F
 
 from . import _lib, engine
+from .region_anim import BlendAnimation, ScaleAnimation, animated_scale, animated_weights
 
 
 @dataclass
@@ -99,11 +100,14 @@ class RegionCropStyler:
     """
 
     def __init__(self, models: Sequence[torch.nn.Module], presets: Sequence[str], masks: torch.Tensor, configs: Sequence[RegionConfig],
-                 padding: int = 64, use_original: bool = True):
+                 padding: int = 64, use_original: bool = True, blend_animations: Optional[Sequence[BlendAnimation]] = None,
+                 scale_animations: Optional[Sequence[ScaleAnimation]] = None):
         self.models, self.presets = list(models), list(presets)
         self.use_original = bool(use_original)
         self.padding = int(padding)
         self.configs = list(configs)
+        self.blend_animations = list(blend_animations) if blend_animations else None      # per region (pipeline.py:1391-1398)
+        self.scale_animations = list(scale_animations) if scale_animations else None      # per region (pipeline.py:1313-1319)
         self.set_masks(masks)
 
     def set_masks(self, masks: torch.Tensor) -> None:
@@ -112,8 +116,9 @@ class RegionCropStyler:
         self.H, self.W = H, W
         self.crops = prepare_region_crops(masks, self.configs, H, W, self.padding)
 
-    def __call__(self, frame_u8: torch.Tensor) -> torch.Tensor:
-        """frame_u8: uint8 [H, W, 3] CUDA.  Returns out01 fp32 [3, H, W], what composite_from_crops returns in the reference."""
+    def __call__(self, frame_u8: torch.Tensor, frame_idx: int = 0) -> torch.Tensor:
+        """frame_u8: uint8 [H, W, 3] CUDA; frame_idx drives the blend / scale animations.  Returns out01 fp32 [3, H, W], what
+        composite_from_crops returns in the reference."""
         if tuple(frame_u8.shape) != (self.H, self.W, 3) or frame_u8.dtype != torch.uint8 or not frame_u8.is_cuda:
             raise ValueError(f"frame_u8 must be a CUDA uint8 [{self.H}, {self.W}, 3] tensor")
         x01 = (frame_u8.permute(2, 0, 1).to(torch.float32) / torch.full((), 255.0, device=frame_u8.device)).contiguous()   # ToTensor, exact
@@ -127,12 +132,21 @@ class RegionCropStyler:
                 x1, y1, x2, y2 = c.padded_bbox
                 ch, cw = y2 - y1, x2 - x1
                 crop = x01[:, y1:y2, x1:x2].unsqueeze(0)
-                if c.config.scale < 1.0:
-                    sh, sw = max(1, int(ch * c.config.scale)), max(1, int(cw * c.config.scale))
+                scale = c.config.scale
+                if self.scale_animations and c.region_idx < len(self.scale_animations):
+                    scale = animated_scale(scale, frame_idx, self.scale_animations[c.region_idx])
+                if scale < 1.0:
+                    sh, sw = max(1, int(ch * scale)), max(1, int(cw * scale))
                     crop = F.interpolate(crop, size=(sh, sw), mode="bilinear", align_corners=False)
                 with torch.no_grad():
                     y = self.models[mi](_pre(crop, self.presets[mi]).contiguous())
                 # (the reference up-scales a down-scaled region back to the box here, pipeline.py:1375-1379; composite_from_crops does exactly
                 # that resize, with the reference's bilinear arithmetic, for any crop whose size differs from its box)
                 styled[mi][c.region_idx] = _post(y, self.presets[mi]).squeeze(0).contiguous()
-        return engine.composite_from_crops(styled, self.crops, x01 if self.use_original else None, self.H, self.W)
+        crops = self.crops
+        if self.blend_animations:                  # composite_from_crops(..., frame_idx, blend_animations) (region_blend.py:2217-2222)
+            crops = [RegionCrop(c.region_idx, c.bbox, c.padded_bbox, c.crop_mask,
+                                RegionConfig(c.config.model_indices, animated_weights(c.config.model_weights, frame_idx, self.blend_animations[c.region_idx])
+                                             if c.region_idx < len(self.blend_animations) else c.config.model_weights, c.config.scale))
+                     for c in self.crops]
+        return engine.composite_from_crops(styled, crops, x01 if self.use_original else None, self.H, self.W)

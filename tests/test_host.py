@@ -154,3 +154,18 @@ def test_param_shape_table_matches_synth():
     for arch in synth.ARCHS:
         sd = synth.make_state_dict(arch, 0)
         assert [(k, tuple(v.shape)) for k, v in sd.items()] == [(k, tuple(sh)) for k, sh in modules.PARAM_SHAPES[arch]]
+
+
+def test_region_animation_scalars_match_the_reference_functions():
+    """Host arithmetic of the blend / scale animations (region_blend.py:1127-1247, 1334-1370) against a table the reference's own
+    functions produced (tests/golden/region_anim.json, written by tests/golden/make_golden_anim.py): exact double equality."""
+    import json
+    from neuralstyletransferv1_b200 import region_anim as ra
+    table = json.load(open(os.path.join(ROOT, "tests", "golden", "region_anim.json")))
+    assert len(table["harmonic"]) >= 190 and len(table["weights"]) >= 60 and len(table["scale"]) >= 20
+    for args, want in table["harmonic"]:
+        assert ra.harmonic_value(*args) == want, args
+    for base, idx, anim, want in table["weights"]:
+        assert ra.animated_weights(base, idx, ra.BlendAnimation(**anim)) == want, (base, idx, anim)
+    for base, idx, anim, want in table["scale"]:
+        assert ra.animated_scale(base, idx, ra.ScaleAnimation(**anim)) == want, (base, idx, anim)
