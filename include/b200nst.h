@@ -200,6 +200,12 @@ int nst_rotate_masks_f32(const float* masks, float* out, int R, int H, int W, do
 int nst_warp_masks_organic_f32(const float* masks, float* out, int R, int H, int W, int mode, double amplitude, double frequency,
                                double time_offset, const double* offsets, float* scratch, void* stream);
 
+/* Replaces: region_blend.feather_mask / gaussian_blur_mask (region_blend.py:69-102) applied to soft masks -- the re-feathering that
+ * blend_by_regions does after a rotation (feather / 2) or an organic warp (max(5, feather / 4)) (region_blend.py:1761-1770): reflect-padded
+ * Gaussian, sigma = feather / 3, separable form (equal to the reference's 2-D kernel to ~1e-6), in place.  masks: [dev] fp32 [R,H,W];
+ * scratch: [dev] R*H*W floats; feather <= 0 is a no-op. */
+int nst_feather_masks_f32(float* masks, int R, int feather, float* scratch, int H, int W, void* stream);
+
 /* Replaces: the reduction of region_blend.compute_mask_bbox (region_blend.py:1969-1994), the first step of prepare_region_crops (:2019-2059),
  * for R masks at once: boxes_dev[4r..4r+3] = (min x, min y, max x, max y) over the pixels with mask > threshold (compared in double, like numpy's
  * fp32 array against the Python float 0.01), or

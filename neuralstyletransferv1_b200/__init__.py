@@ -8,8 +8,8 @@ Public surface (mirrors the reference's):
 from .engine import (Engine, composite_from_crops, composite_regions, composite_regions_batch, flow_ema,  # noqa: F401
                      io_preset_affine)
 from .frame_pipeline import FramePipeline, MultiGpuFramePipeline  # noqa: F401
-from .region_masks import (MorphAnimation, generate_region_masks, rotate_all_masks, voronoi_masks,  # noqa: F401
-                           warp_all_masks_organic)
+from .region_masks import (MorphAnimation, RegionBlender, assign_models_to_regions, feather_masks, generate_region_masks,  # noqa: F401
+                           rotate_all_masks, voronoi_masks, warp_all_masks_organic)
 from .temporal import LabEma, motion_blend  # noqa: F401
 from .post_chain import PostChain  # noqa: F401
 from .region_anim import BlendAnimation, ScaleAnimation, animated_scale, animated_weights, harmonic_value  # noqa: F401
@@ -20,5 +20,5 @@ from .sharding import shard_range, shard_sizes  # noqa: F401
 
 __all__ = ["Engine", "composite_regions", "composite_regions_batch", "composite_from_crops", "flow_ema", "FramePipeline",
            "MultiGpuFramePipeline", "voronoi_masks", "generate_region_masks", "rotate_all_masks", "warp_all_masks_organic",
-           "MorphAnimation", "LabEma", "motion_blend", "PostChain", "BlendAnimation", "ScaleAnimation", "animated_scale", "animated_weights", "harmonic_value", "RegionConfig", "RegionCrop", "RegionCropStyler", "mask_bboxes", "prepare_region_crops", "io_preset_affine", "TransformerNet", "TransformerNetNST",
+           "MorphAnimation", "RegionBlender", "assign_models_to_regions", "feather_masks", "LabEma", "motion_blend", "PostChain", "BlendAnimation", "ScaleAnimation", "animated_scale", "animated_weights", "harmonic_value", "RegionConfig", "RegionCrop", "RegionCropStyler", "mask_bboxes", "prepare_region_crops", "io_preset_affine", "TransformerNet", "TransformerNetNST",
            "ReCoNet", "ReCoNetModel", "shard_range", "shard_sizes"]

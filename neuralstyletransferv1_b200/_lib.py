@@ -51,6 +51,7 @@ PROTOTYPES = {
     "nst_rotate_masks_f32": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_double, C.c_void_p]),
     "nst_warp_masks_organic_f32": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_double, C.c_double, C.c_double,
                                              C.POINTER(C.c_double), C.c_void_p, C.c_void_p]),
+    "nst_feather_masks_f32": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
     "nst_mask_bboxes": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_double, C.c_void_p, C.c_void_p]),
     "nst_mask_scratch_floats": (C.c_size_t, [C.c_int, C.c_int, C.c_int]),
     "nst_lab_ema_u8": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,

@@ -1493,11 +1493,17 @@ int nst::feather_labels(const uint8_t* label, int R, int feather, float* masks, 
     for (int t = 0; t < k; ++t) b.w[t] /= sum;
     b.k = k;
   }
-  b.label = label; b.src = nullptr; b.dst = tmp; b.vertical = 0;
+  b.label = label; b.src = label ? nullptr : masks; b.dst = tmp; b.vertical = 0;       // label == null: feather the soft masks in place
   CUDA_TRY(launch_blur_pass(b, st));
   b.label = nullptr; b.src = tmp; b.dst = masks; b.vertical = 1;
   CUDA_TRY(launch_blur_pass(b, st));
   return NST_OK;
+}
+
+extern "C" int nst_feather_masks_f32(float* masks, int R, int feather, float* scratch, int H, int W, void* stream) {
+  if (!masks || !scratch || R < 1 || H < 2 || W < 2) return fail(NST_ERR_INVALID, "feather_masks: null / empty argument");
+  if (feather <= 0) return NST_OK;                                       // feather_mask returns its argument
+  return feather_labels(nullptr, R, feather, masks, scratch, H, W, (cudaStream_t)stream, "feather_masks");
 }
 
 extern "C" int nst_voronoi_masks_f32(const float* points_xy, const float* region_weights, int R, int feather, float* masks, float* scratch,

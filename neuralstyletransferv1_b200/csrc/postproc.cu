@@ -454,7 +454,7 @@ __global__ void __launch_bounds__(256) voronoi_label_kernel(const __grid_constan
   }
 }
 struct BlurArgs {
-  const uint8_t* label;     // horizontal pass input (label == r is the hard mask), or null
+  const uint8_t* label;     // horizontal pass input (label == r is the hard mask), or null: the horizontal pass reads src (soft masks)
   const float* src;         // vertical pass input [R,H,W]
   float* dst;               // [R,H,W]
   int R, H, W, k, vertical;
@@ -476,7 +476,7 @@ __global__ void __launch_bounds__(256) blur_pass_kernel(const __grid_constant__ 
     if (!a.vertical) {
       for (int t = 0; t < a.k; ++t) {
         const int xx = reflect_idx(x + t - pad, a.W);
-        acc = fmaf(a.w[t], a.label[(size_t)y * a.W + xx] == r ? 1.f : 0.f, acc);
+        acc = fmaf(a.w[t], a.label ? (a.label[(size_t)y * a.W + xx] == r ? 1.f : 0.f) : a.src[(size_t)r * hw + (size_t)y * a.W + xx], acc);
       }
     } else {
       const float* pl = a.src + (size_t)r * hw;

@@ -279,3 +279,87 @@ def warp_all_masks_organic(masks: torch.Tensor, morph: MorphAnimation, frame_idx
                                             torch.cuda.current_stream(masks.device).cuda_stream)
     _lib.check(rc, "nst_warp_masks_organic_f32")
     return out
+
+
+def feather_masks(masks: torch.Tensor, feather_px: int) -> torch.Tensor:
+    """feather_mask (region_blend.py:97-102) of soft masks, in place on a fresh copy: reflect-padded Gaussian, sigma = feather / 3."""
+    masks = _check_masks(masks, "feather_masks")
+    if feather_px <= 0:
+        return masks
+    lib = _lib.load()
+    R, H, W = masks.shape
+    out = masks.clone()
+    scratch = torch.empty(R * H * W, dtype=torch.float32, device=masks.device)
+    with torch.cuda.device(masks.device):
+        rc = lib.nst_feather_masks_f32(out.data_ptr(), R, int(feather_px), scratch.data_ptr(), H, W, torch.cuda.current_stream(masks.device).cuda_stream)
+    _lib.check(rc, "nst_feather_masks_f32")
+    return out
+
+
+def assign_models_to_regions(num_regions: int, num_models: int, assignment: str = "random", weights: Optional[Sequence[float]] = None,
+                             seed: Optional[int] = None, original_chance: float = 0.0) -> List[int]:
+    """Which model styles which region; -1 = the original frame (region_blend.py:983-1046, same `random.Random` draws)."""
+    rng = random.Random() if seed is None else random.Random(seed)
+    pool = list(range(num_models)) + ([-1] if original_chance > 0 else [])
+    if assignment == "sequential":
+        return [pool[i % len(pool)] for i in range(num_regions)]
+    if assignment == "random":
+        out = []
+        for _ in range(num_regions):
+            out.append(-1 if (original_chance > 0 and rng.random() < original_chance) else rng.randint(0, num_models - 1))
+        return out
+    if assignment == "weighted":
+        w = list(weights[:num_models]) if weights is not None else [1.0 / num_models] * num_models
+        total = sum(w)
+        if original_chance > 0:
+            return rng.choices(pool, weights=[(x / total) * (1.0 - original_chance) for x in w] + [original_chance], k=num_regions)
+        return rng.choices(range(num_models), weights=[x / total for x in w], k=num_regions)
+    raise ValueError(f"Unknown assignment mode: {assignment}")
+
+
+class RegionBlender:
+    """region_blend.blend_by_regions (region_blend.py:1690-1787) for batches of frames on the device: base masks from the pattern generator
+    (kept for the clip), per-frame rotation (+ re-feather by feather / 2) and organic morph (+ re-feather by max(5, feather / 4)), model
+    assignment, one batched composite launch (engine.composite_regions_batch)."""
+
+    def __init__(self, num_models: int, H: int, W: int, mode: str = "voronoi", region_count: Optional[int] = None, assignment: str = "random",
+                 weights: Optional[Sequence[float]] = None, feather: int = 20, seed: Optional[int] = None, original_chance: float = 0.0,
+                 rotation_rate: float = 0.0, morph: Optional[MorphAnimation] = None, device="cuda:0"):
+        self.num_models, self.H, self.W, self.mode = int(num_models), H, W, mode
+        self.region_count = region_count if region_count is not None else self.num_models
+        self.assignment, self.weights, self.feather, self.seed = assignment, weights, int(feather), seed
+        self.original_chance, self.rotation_rate, self.morph, self.device = float(original_chance), float(rotation_rate), morph, device
+        self.animated = self.rotation_rate != 0 or bool(morph and morph.enabled)
+        self._base = None
+        self._assignments: Optional[List[int]] = None
+
+    def _fresh(self):
+        masks = generate_region_masks(self.H, self.W, self.mode, self.region_count, self.seed, self.feather, device=self.device)
+        return masks, assign_models_to_regions(masks.shape[0], self.num_models, self.assignment, self.weights, self.seed, self.original_chance)
+
+    def masks_at(self, frame_idx: int):
+        """(masks fp32 [R, H, W], assignments) of one frame.  Animated clips and seeded static ones keep their base masks (the reference's
+        mask cache, and its regeneration with the same seed); an unseeded static clip draws new masks every frame, like the reference."""
+        if self._base is None or (not self.animated and self.seed is None):
+            self._base, self._assignments = self._fresh()
+        masks = self._base
+        if self.rotation_rate != 0:
+            masks = feather_masks(rotate_all_masks(masks, frame_idx * self.rotation_rate), self.feather // 2)
+        if self.morph and self.morph.enabled:
+            masks = feather_masks(warp_all_masks_organic(masks, self.morph, frame_idx), max(5, self.feather // 4))
+        return masks, self._assignments
+
+    def __call__(self, styled: Sequence[torch.Tensor], original: Optional[torch.Tensor] = None, frame_idx: int = 0) -> torch.Tensor:
+        """styled: one uint8 [N, H, W, 3] CUDA batch per model (consecutive frames frame_idx .. frame_idx + N - 1); original: the same
+        for the unstyled frames.  Returns the composited uint8 [N, H, W, 3] batch."""
+        from . import engine
+        N = styled[0].shape[0]
+        if not self.animated and self.seed is not None:
+            masks, assign = self.masks_at(frame_idx)
+        else:
+            per = [self.masks_at(frame_idx + i) for i in range(N)]
+            masks, assign = torch.stack([p[0] for p in per]), per[-1][1]
+            if any(p[1] != assign for p in per):          # unseeded random assignment differs per frame: composite frame by frame
+                return torch.cat([engine.composite_regions_batch([s[i:i + 1] for s in styled], per[i][0], [[a] for a in per[i][1]],
+                                                                 original=original[i:i + 1] if original is not None else None) for i in range(N)])
+        return engine.composite_regions_batch(list(styled), masks, [[a] for a in assign], original=original)

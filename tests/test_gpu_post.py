@@ -289,3 +289,24 @@ def test_region_crops_bboxes_and_crop_styling():
     strip = (rmasks.sum(0) < 0.1).cpu()                                               # the uncovered strip is the original, exactly
     x01 = frame.permute(2, 0, 1).float() / 255.0
     assert strip.any() and torch.equal(got01[:, strip], x01[:, strip])
+
+
+def test_region_crop_styler_animations_are_the_static_path_with_animated_scalars():
+    """blend / scale animations only change the per-frame weights and scales handed to the same kernels: frame 7 of an animated styler is
+    bit-identical to a static styler configured with animated_weights / animated_scale of frame 7."""
+    import neuralstyletransferv1_b200 as m
+    H, W = 120, 160
+    masks = m.generate_region_masks(H, W, "voronoi", 2, seed=3, feather=4)
+    mod = m.TransformerNet().to("cuda:0")
+    mod.load_state_dict(synth.make_state_dict("johnson", 0))
+    mod.eval()
+    cfgs = [m.RegionConfig([0, -1], [0.7, 0.3], 1.0), m.RegionConfig([0], [1.0], 1.0)]
+    ba = [m.BlendAnimation(enabled=True, period=20.0, min_opacity=0.1, max_opacity=1.0), m.BlendAnimation(enabled=False)]
+    sa = [m.ScaleAnimation(enabled=False), m.ScaleAnimation(enabled=True, period=30.0, min_scale=0.5, max_scale=0.9, waveform="triangle")]
+    frame = synth.synthetic_frames_u8(1, H, W, seed=4)[0].cuda()
+    animated = m.RegionCropStyler([mod], ["raw_255"], masks, cfgs, padding=16, blend_animations=ba, scale_animations=sa)(frame, frame_idx=7)
+    w7 = m.animated_weights([0.7, 0.3], 7, ba[0])
+    s7 = m.animated_scale(1.0, 7, sa[1])
+    assert w7 != [0.7, 0.3] and s7 < 1.0
+    static = m.RegionCropStyler([mod], ["raw_255"], masks, [m.RegionConfig([0, -1], w7, 1.0), m.RegionConfig([0], [1.0], s7)], padding=16)(frame)
+    assert torch.equal(animated, static)

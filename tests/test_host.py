@@ -169,3 +169,13 @@ def test_region_animation_scalars_match_the_reference_functions():
         assert ra.animated_weights(base, idx, ra.BlendAnimation(**anim)) == want, (base, idx, anim)
     for base, idx, anim, want in table["scale"]:
         assert ra.animated_scale(base, idx, ra.ScaleAnimation(**anim)) == want, (base, idx, anim)
+
+
+def test_model_assignments_match_the_reference_function():
+    """assign_models_to_regions (region_blend.py:983-1046): same `random.Random` draws, same lists."""
+    import json
+    from neuralstyletransferv1_b200.region_masks import assign_models_to_regions
+    table = json.load(open(os.path.join(ROOT, "tests", "golden", "region_assignments.json")))
+    assert len(table) >= 100
+    for (nr, nm, mode, w, seed, oc), want in table:
+        assert assign_models_to_regions(nr, nm, mode, w, seed, oc) == want, (nr, nm, mode, seed, oc)
