@@ -256,7 +256,9 @@ def run_b200(args):
     host_out = torch.empty_like(host_in).pin_memory()
     d_in = host_in.to(dev, non_blocking=True)
     d_out = torch.empty_like(d_in)
-    masks = nst.voronoi_masks(H, W, 4, seed=42, feather=20, device=dev) if region else None      # region_blend.py:925; pipeline.py:1126-1127,1152
+    # region_blend.blend_by_regions with the reference's defaults for this config: voronoi, 4 regions, seed 42, feather 20, models assigned
+    # A, B, C, D in sequence (region_blend.py:925,1690; pipeline.py:1126-1127,1152) -- masks made on the device, kept for the clip
+    blender = nst.RegionBlender(4, H, W, mode="voronoi", region_count=4, assignment="sequential", feather=20, seed=42, device=dev) if region else None
     styled = [torch.empty_like(d_in) for _ in range(n_models)] if region else None
     torch.cuda.synchronize()
     comp_ev = []
@@ -271,7 +273,7 @@ def run_b200(args):
         if time_composite:
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record()
-        nst.composite_regions_batch(styled, masks, [[0], [1], [2], [3]], original=d_in, out=d_out)     # sequential A,B,C,D assignment
+        blender(styled, original=d_in, out=d_out)
         if time_composite:
             e1.record()
             comp_ev.append((e0, e1))
@@ -314,7 +316,7 @@ def run_b200(args):
         x = host_in.to(dev, non_blocking=True)
         for k in range(n_models):
             models[k].stylize_u8(x, preset, out=styled[k])
-        nst.composite_regions_batch(styled, masks, [[0], [1], [2], [3]], original=x, out=d_out)
+        blender(styled, original=x, out=d_out)
         host_out.copy_(d_out, non_blocking=True)
         torch.cuda.synchronize()
 
@@ -395,7 +397,7 @@ def run_b200(args):
                    "parallelism": f"frame-batch sharding over {world} GPU(s), no collective ({'contiguous split of a fixed clip' if strong else 'fixed batch per GPU'})"},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": F_total * H * W * 3, "d2h_bytes_per_step": F_total * H * W * 3,
                 "api": "neuralstyletransferv1_b200.FramePipeline (pinned host in -> chunked H2D | stylize_u8 | D2H on three streams -> pinned host out)"
-                       if not region else "host frames -> H2D -> 4 x stylize_u8 -> composite_regions_batch -> D2H"},
+                       if not region else "host frames -> H2D -> 4 x stylize_u8 -> RegionBlender (composite_regions_batch) -> D2H"},
         "gpu_launches": launches,
         "clocks": clk.summary(),
         "roofline": roofline,

@@ -349,7 +349,8 @@ class RegionBlender:
             masks = feather_masks(warp_all_masks_organic(masks, self.morph, frame_idx), max(5, self.feather // 4))
         return masks, self._assignments
 
-    def __call__(self, styled: Sequence[torch.Tensor], original: Optional[torch.Tensor] = None, frame_idx: int = 0) -> torch.Tensor:
+    def __call__(self, styled: Sequence[torch.Tensor], original: Optional[torch.Tensor] = None, frame_idx: int = 0,
+                 out: Optional[torch.Tensor] = None) -> torch.Tensor:
         """styled: one uint8 [N, H, W, 3] CUDA batch per model (consecutive frames frame_idx .. frame_idx + N - 1); original: the same
         for the unstyled frames.  Returns the composited uint8 [N, H, W, 3] batch."""
         from . import engine
@@ -360,6 +361,7 @@ class RegionBlender:
             per = [self.masks_at(frame_idx + i) for i in range(N)]
             masks, assign = torch.stack([p[0] for p in per]), per[-1][1]
             if any(p[1] != assign for p in per):          # unseeded random assignment differs per frame: composite frame by frame
-                return torch.cat([engine.composite_regions_batch([s[i:i + 1] for s in styled], per[i][0], [[a] for a in per[i][1]],
-                                                                 original=original[i:i + 1] if original is not None else None) for i in range(N)])
-        return engine.composite_regions_batch(list(styled), masks, [[a] for a in assign], original=original)
+                res = torch.cat([engine.composite_regions_batch([s[i:i + 1] for s in styled], per[i][0], [[a] for a in per[i][1]],
+                                                                original=original[i:i + 1] if original is not None else None) for i in range(N)])
+                return res if out is None else out.copy_(res)
+        return engine.composite_regions_batch(list(styled), masks, [[a] for a in assign], original=original, out=out)
