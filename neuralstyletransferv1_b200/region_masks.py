@@ -324,12 +324,16 @@ class RegionBlender:
 
     def __init__(self, num_models: int, H: int, W: int, mode: str = "voronoi", region_count: Optional[int] = None, assignment: str = "random",
                  weights: Optional[Sequence[float]] = None, feather: int = 20, seed: Optional[int] = None, original_chance: float = 0.0,
-                 rotation_rate: float = 0.0, morph: Optional[MorphAnimation] = None, device="cuda:0"):
+                 rotation_rate: float = 0.0, morph: Optional[MorphAnimation] = None, device="cuda:0", configs=None):
         self.num_models, self.H, self.W, self.mode = int(num_models), H, W, mode
         self.region_count = region_count if region_count is not None else self.num_models
         self.assignment, self.weights, self.feather, self.seed = assignment, weights, int(feather), seed
         self.original_chance, self.rotation_rate, self.morph, self.device = float(original_chance), float(rotation_rate), morph, device
         self.animated = self.rotation_rate != 0 or bool(morph and morph.enabled)
+        # blend_by_regions_advanced (region_blend.py:1832-1957): per-region model blends instead of one model per region.  configs: one
+        # object per region with `model_indices` / `model_weights` (region_crops.RegionConfig, or the reference's own RegionConfig, which
+        # `parse_region_configs` builds from the CLI's blend / scale strings -- that parsing stays in the reference's CLI layer)
+        self.configs = list(configs) if configs is not None else None
         self._base = None
         self._assignments: Optional[List[int]] = None
 
@@ -364,4 +368,7 @@ class RegionBlender:
                 res = torch.cat([engine.composite_regions_batch([s[i:i + 1] for s in styled], per[i][0], [[a] for a in per[i][1]],
                                                                 original=original[i:i + 1] if original is not None else None) for i in range(N)])
                 return res if out is None else out.copy_(res)
+        if self.configs is not None:
+            return engine.composite_regions_batch(list(styled), masks, [list(c.model_indices) for c in self.configs],
+                                                  [list(c.model_weights) for c in self.configs], original=original, out=out)
         return engine.composite_regions_batch(list(styled), masks, [[a] for a in assign], original=original, out=out)

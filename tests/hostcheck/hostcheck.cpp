@@ -155,4 +155,12 @@ void hc_motion_blend(const uint8_t* styled, const uint8_t* original, const float
   }
 }
 
+void hc_blend_pack(const uint8_t* styled, const uint8_t* original, const float* mask, double blend, int composite_mode, uint8_t* out, size_t npix) {
+  const bool on = blend >= 0.0 && blend < 1.0;
+  for (size_t i = 0; i < npix; ++i)
+    for (int c = 0; c < 3; ++c)
+      out[i * 3 + c] = blend_pack_u8(styled[i * 3 + c], original[i * 3 + c], mask != nullptr, mask ? mask[i] : 0.f, composite_mode, on ? (float)blend : 2.f,
+                                     (float)(1.0 - blend));
+}
+
 }  // extern "C"

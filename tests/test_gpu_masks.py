@@ -207,3 +207,22 @@ def test_region_blender_matches_blend_by_regions(name):
     want = g["out_" + name].astype(int)
     d = np.abs(got - want)
     assert d.max() <= 1 and (d > 0).mean() < 0.05, (int(d.max()), float((d > 0).mean()))
+
+
+def test_region_blender_with_per_region_model_blends():
+    """blend_by_regions_advanced's composite (region_blend.py:1832-1957 -> composite_regions_advanced): the blender with RegionConfigs is
+    the batched composite with those indices / weights over the blender's own masks."""
+    import neuralstyletransferv1_b200 as m
+    from neuralstyletransferv1_b200 import engine
+    g = np.load(os.path.join(GOLDEN, "blend_by_regions_60x84.npz"))
+    styled = [torch.from_numpy(g[f"styled{k}"]).cuda() for k in range(3)]
+    orig = torch.from_numpy(g["orig"]).cuda()
+    cfgs = [m.RegionConfig([0, 1], [0.7, 0.3]), m.RegionConfig([1, -1], [0.5, 0.5]), m.RegionConfig([2], [1.0]), m.RegionConfig([2, 0], [0.2, 0.8])]
+    blender = m.RegionBlender(3, 60, 84, mode="voronoi", region_count=4, feather=6, seed=42, configs=cfgs)
+    got = blender(styled, orig, frame_idx=0)
+    masks = m.generate_region_masks(60, 84, "voronoi", 4, seed=42, feather=6)
+    want = engine.composite_regions_batch(styled, masks, [c.model_indices for c in cfgs], [c.model_weights for c in cfgs], original=orig)
+    assert torch.equal(got, want)
+    ref = O.composite_regions_advanced([s[0].cpu().permute(2, 0, 1).float() / 255 for s in styled], [mk[None, None] for mk in masks.cpu()],
+                                       [c.model_indices for c in cfgs], [c.model_weights for c in cfgs], orig[0].cpu().permute(2, 0, 1).float() / 255)
+    assert torch.equal(got[0].cpu(), O.pack_u8(ref[None])[0])

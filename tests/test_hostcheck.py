@@ -111,3 +111,25 @@ def test_lab_ema_and_motion_blend_follow_the_reference(hc):
                            _p(out), _p(amap), H, W, C.c_double(float(m["blend"])), C.c_double(0.40), C.c_double(8.0), C.c_double(3.0))
         assert np.array_equal(amap, m[f"alpha_map_{t}"]), t           # cv2.GaussianBlur's fp32 order, SIMD tails included
         assert np.array_equal(out, m[f"out_{t}"]), t
+
+
+def test_blend_pack_follows_the_reference_arithmetic(hc):
+    """The uint8 blend stage (to_tensor -> mask composite -> uniform blend -> ToPILImage, pipeline.py:1981, 2040-2043, 2088-2094) against
+    the oracle's torch expression of the same lines, every uint8 pair included."""
+    import torch
+    from oracle import nst_oracle as O
+    rng = np.random.default_rng(5)
+    H, W = 64, 256 * 4
+    styled = rng.integers(0, 256, (H, W, 3), dtype=np.uint8)
+    orig = rng.integers(0, 256, (H, W, 3), dtype=np.uint8)
+    styled[0, :, 0] = np.repeat(np.arange(256, dtype=np.uint8), 4)           # a sweep of every level against random originals
+    mask = rng.random((H, W), dtype=np.float32)
+    mask[:4] = 0.0
+    mask[4:8] = 1.0
+    s01 = torch.from_numpy(styled).permute(2, 0, 1).float().div(255)[None]
+    x01 = torch.from_numpy(orig).permute(2, 0, 1).float().div(255)[None]
+    for blend, use_mask, mode in ((0.8, False, 0), (1.0, True, 0), (0.6, True, 1), (0.0, True, 0), (-1.0, False, 0), (0.35, True, 1)):
+        out = np.empty_like(styled)
+        hc.hc_blend_pack(_p(styled), _p(orig), _p(mask) if use_mask else None, C.c_double(blend), mode, _p(out), C.c_size_t(H * W))
+        want = O.post_u8(s01, x01, blend, torch.from_numpy(mask)[None] if use_mask else None, "keep" if mode == 0 else "replace")[0].numpy()
+        assert np.array_equal(out, want), (blend, use_mask, mode)
