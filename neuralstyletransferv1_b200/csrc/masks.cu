@@ -113,14 +113,55 @@ struct OrganicArgs {
   int R, H, W, mode;
   double freq, time_offset, max_disp_d; float max_disp;      // max_disp: fp32 against the fp32 noise flow, fp64 against the analytic flows
   double off[PAT_MAX_R * 8];            // per region: field x (octave 0: ox, oy; octave 1: ox, oy), field y (same)
+  double* tab;                          // [2R planes][2 octaves][5 W + 5 H] column / row trig tables (organic_tables_kernel)
 };
+// The noise of _simplex_noise_2d is, per octave,  sin(X1) cos(Y1) + 0.5 sin(X2 + Y2) + 0.3 cos(X3 - Y3)  with X* functions of the column and
+// Y* of the row only (np.linspace grids).  Evaluating three double-precision sin / cos per octave and pixel made this the slowest kernel of
+// the library (B200's fp64 rate: 0.94 ms per 1080p mask set); instead the 10 column- and row-functions are tabulated once per launch
+// (organic_tables_kernel: (5 W + 5 H) trig evaluations per plane and octave) and the pixel combines them with the angle-addition identities
+// -- 5 fp64 multiplies and 4 adds per octave.  sin(X2 + Y2) computed as sin X2 cos Y2 + cos X2 sin Y2 differs from numpy's
+// sin(fl(X2 + Y2)) by ~1e-13 (arguments reach 1e3), which moves the fp32-narrowed noise by one ulp about twice per million values; after the
+// 1/32-pixel quantisation of the map that is an isolated pixel per several frames (tests allow 8 of 5040 / 64 of 2 M; measured: none).
+constexpr int ORG_TAB = 10;     // per (plane, octave): x tables [5][W] then y tables [5][H]
+__global__ void __launch_bounds__(256) organic_tables_kernel(const __grid_constant__ OrganicArgs a) {
+  const int rf = blockIdx.y >> 1, o = blockIdx.y & 1;                           // plane = region * 2 + field; two octaves
+  const double fm = o ? 2.0 : 1.0, ox = a.off[rf * 4 + 2 * o], oy = a.off[rf * 4 + 2 * o + 1];
+  double* tx = a.tab + (size_t)blockIdx.y * 5 * (a.W + a.H);
+  double* ty = tx + 5 * (size_t)a.W;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < a.W + a.H; i += gridDim.x * blockDim.x) {
+    if (i < a.W) {
+      const double xx = linspace_at(a.freq, a.W, i);
+      const double x1 = dadd(dmul(xx, fm), ox), x2 = dadd(dmul(dmul(xx, fm), 0.7), dmul(ox, 0.8)), x3 = dadd(dmul(dmul(xx, fm), 0.5), dmul(oy, 0.6));
+      tx[i] = sin(x1); tx[a.W + i] = sin(x2); tx[2 * a.W + i] = cos(x2); tx[3 * a.W + i] = cos(x3); tx[4 * a.W + i] = sin(x3);
+    } else {
+      const int j = i - a.W;
+      const double yy = linspace_at(a.freq, a.H, j);
+      const double y1 = dadd(dmul(yy, fm), oy), y2 = dmul(dmul(yy, fm), 0.7), y3 = dmul(dmul(yy, fm), 0.5);
+      ty[j] = cos(y1); ty[a.H + j] = cos(y2); ty[2 * a.H + j] = sin(y2); ty[3 * a.H + j] = cos(y3); ty[4 * a.H + j] = sin(y3);
+    }
+  }
+}
 __global__ void __launch_bounds__(256) organic_noise_kernel(const __grid_constant__ OrganicArgs a) {
   const int hw = a.H * a.W;
   const int rf = blockIdx.y;                                                  // region * 2 + field
   float lo = INFINITY, hi = -INFINITY;
   for (int pix = blockIdx.x * blockDim.x + threadIdx.x; pix < hw; pix += gridDim.x * blockDim.x) {
     const int y = pix / a.W, x = pix - y * a.W;
-    const float v = simplex_raw(linspace_at(a.freq, a.W, x), linspace_at(a.freq, a.H, y), a.off + rf * 4, 2);
+    float result = 0.f;
+    double amplitude = 1.0, total = 0.0;
+#pragma unroll
+    for (int o = 0; o < 2; ++o) {
+      const double* tx = a.tab + (size_t)(rf * 2 + o) * 5 * (a.W + a.H);
+      const double* ty = tx + 5 * (size_t)a.W;
+      const double t1 = dmul(tx[x], ty[y]);
+      const double t2 = dadd(dmul(tx[a.W + x], ty[a.H + y]), dmul(tx[2 * a.W + x], ty[2 * a.H + y]));          // sin(X2 + Y2)
+      const double t3 = dadd(dmul(tx[3 * a.W + x], ty[3 * a.H + y]), dmul(tx[4 * a.W + x], ty[4 * a.H + y]));  // cos(X3 - Y3)
+      const double noise = dadd(dadd(t1, dmul(t2, 0.5)), dmul(t3, 0.3));
+      result = (float)dadd((double)result, dmul(noise, amplitude));             // fp32 array += fp64 array
+      total += amplitude;
+      amplitude *= 0.5;
+    }
+    const float v = div(result, (float)total);
     a.raw[(size_t)rf * hw + pix] = v;
     lo = fminf(lo, v); hi = fmaxf(hi, v);
   }
@@ -299,6 +340,10 @@ extern "C" int nst_rotate_masks_f32(const float* masks, float* out, int R, int H
   return NST_OK;
 }
 
+// floats of scratch in front of the trig tables, rounded up so that the tables are 8-byte aligned (the scratch base is a cudaMalloc /
+// torch allocation: at least 256-byte aligned)
+static size_t organic_table_offset_floats(int R, size_t hw) { return (4 * PAT_MAX_R + 8 + 3 * (size_t)R * hw + (hw + 3) / 4 + 1) & ~(size_t)1; }
+
 extern "C" int nst_warp_masks_organic_f32(const float* masks, float* out, int R, int H, int W, int mode, double amplitude, double frequency,
                                           double time_offset, const double* offsets, float* scratch, void* stream) {
   if (!masks || !out || !scratch || masks == out || R < 1 || R > PAT_MAX_R || H < 2 || W < 2 || mode < ORG_BLOB || mode > ORG_PULSE)
@@ -307,7 +352,7 @@ extern "C" int nst_warp_masks_organic_f32(const float* masks, float* out, int R,
   if (noisy && offsets == nullptr) return api_fail(NST_ERR_INVALID, "warp_masks_organic: blob / tentacle need the 8 noise offsets of every region");
   cudaStream_t st = (cudaStream_t)stream;
   const size_t hw = (size_t)H * W;
-  // scratch: [4R floats min/max][8 ints counters][2R*H*W floats noise][R*H*W floats fill temporary][H*W bytes gap map]
+  // scratch: [4R floats min/max][8 ints counters][2R*H*W floats noise][R*H*W floats fill temporary][H*W bytes gap map][trig tables, doubles]
   OrganicArgs a;
   memset(&a, 0, sizeof(a));
   a.in = masks; a.warped = out; a.R = R; a.H = H; a.W = W; a.mode = mode;
@@ -316,13 +361,17 @@ extern "C" int nst_warp_masks_organic_f32(const float* masks, float* out, int R,
   a.raw = scratch + 4 * PAT_MAX_R + 8;
   float* tmp = a.raw + 2 * (size_t)R * hw;
   a.gap = reinterpret_cast<uint8_t*>(tmp + (size_t)R * hw);
+  a.tab = reinterpret_cast<double*>(scratch + organic_table_offset_floats(R, hw));
   a.freq = mode == ORG_TENTACLE ? frequency * 2 : frequency;              // region_blend.py:693
   a.time_offset = time_offset;
   a.max_disp_d = std::max(H, W) * amplitude;
   a.max_disp = (float)a.max_disp_d;                       // :720; numpy narrows the Python float against fp32 arrays
   if (noisy) memcpy(a.off, offsets, sizeof(double) * 8 * R);
   init_minmax_kernel<<<1, 64, 0, st>>>(a.mm, 2 * R, a.counters, 8);
-  if (noisy) organic_noise_kernel<<<dim3(grid_for((int)hw), 2 * R), 256, 0, st>>>(a);
+  if (noisy) {
+    organic_tables_kernel<<<dim3((W + H + 255) / 256, 4 * R), 256, 0, st>>>(a);
+    organic_noise_kernel<<<dim3(grid_for((int)hw), 2 * R), 256, 0, st>>>(a);
+  }
   organic_warp_kernel<<<grid_for((int)hw), 256, 0, st>>>(a);
   const int ks[4] = {5, 11, 21, 41};
   for (int p = 0; p < 4; ++p) {
@@ -340,7 +389,7 @@ extern "C" int nst_warp_masks_organic_f32(const float* masks, float* out, int R,
 extern "C" size_t nst_mask_scratch_floats(int R, int H, int W) {
   const size_t hw = (size_t)H * W;
   const size_t pattern = 4 + hw + (hw + 3) / 4 + (size_t)R * hw;
-  const size_t organic = 4 * PAT_MAX_R + 8 + 3 * (size_t)R * hw + (hw + 3) / 4;
+  const size_t organic = organic_table_offset_floats(R, hw) + 2 * (size_t)(4 * R) * 5 * (W + H);      // tables are doubles
   return std::max(pattern, organic);
 }
 

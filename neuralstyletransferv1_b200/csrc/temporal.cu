@@ -55,12 +55,23 @@ struct MotionBlendArgs {
   float max_alpha, alpha_span;        // fp32(blend), fp32(blend - MIN_ALPHA)
   float kern[MB_MAX_K];
 };
+// Row pass: one block = 256 consecutive pixels of one row.  The clipped flow magnitude of the segment and its 2 * (k / 2) neighbours is computed
+// ONCE into shared memory (the per-pixel form evaluated sqrt + division for each of the k taps: 25x redundant at sigma 3), then every thread
+// runs the same tap sequence as before -- bit-identical.
 __global__ void __launch_bounds__(256) motion_row_kernel(const __grid_constant__ MotionBlendArgs a) {
-  const int hw = a.H * a.W;
-  for (int pix = blockIdx.x * blockDim.x + threadIdx.x; pix < hw; pix += gridDim.x * blockDim.x) {
-    const int y = pix / a.W, x = pix - y * a.W;
-    a.rowf[pix] = motion_row_at(a.flow, a.W, y, x, a.kern, a.k, a.norm_div);
+  __shared__ float sm[256 + MB_MAX_K];
+  const int pad = a.k / 2, y = blockIdx.y, x0 = blockIdx.x * 256;
+  for (int i = threadIdx.x; i < 256 + 2 * pad; i += 256) {
+    const int xx = reflect101(x0 + i - pad, a.W);                    // (columns beyond the row's end are never read by a live thread)
+    sm[i] = motion_m(a.flow, (size_t)y * a.W + xx, a.norm_div);
   }
+  __syncthreads();
+  const int x = x0 + threadIdx.x;
+  if (x >= a.W) return;
+  const bool fma_path = x < (a.W & ~3);
+  float acc = mul(sm[threadIdx.x], a.kern[0]);
+  for (int t = 1; t < a.k; ++t) acc = fma_path ? fmaf(sm[threadIdx.x + t], a.kern[t], acc) : add(acc, mul(sm[threadIdx.x + t], a.kern[t]));
+  a.rowf[(size_t)y * a.W + x] = acc;
 }
 __global__ void __launch_bounds__(256) motion_col_blend_kernel(const __grid_constant__ MotionBlendArgs a) {
   const int hw = a.H * a.W;
@@ -126,7 +137,7 @@ extern "C" int nst_motion_blend_u8(const uint8_t* styled, const uint8_t* origina
   a.norm_div = (float)motion_norm;
   a.max_alpha = (float)blend; a.alpha_span = (float)(blend - min_alpha);
   cudaStream_t st = (cudaStream_t)stream;
-  motion_row_kernel<<<grid_for(H * W), 256, 0, st>>>(a);
+  motion_row_kernel<<<dim3((W + 255) / 256, H), 256, 0, st>>>(a);
   motion_col_blend_kernel<<<grid_for(H * W), 256, 0, st>>>(a);
   NST_CUDA_TRY(cudaGetLastError());
   return NST_OK;
