@@ -86,8 +86,49 @@ __global__ void __launch_bounds__(256) resize_post_pack_kernel(const __grid_cons
   }
 }
 
+// Identity size (the frame already has the content size: every multiple-of-4 frame, and the pack stage of post_chain.PostChain), H*W a multiple
+// of 4: four pixels per thread -- three 16-byte plane loads, 12 bytes of original, one 16-byte mask load, three 32-bit stores.  The bilinear
+// weights of an identity resize are exactly (1, 0), so the resized value IS the source value: same bytes as the general kernel.
+__global__ void __launch_bounds__(256) post_pack_x4_kernel(const __grid_constant__ ResizePackArgs a) {
+  const size_t hw = (size_t)a.H * a.W, quads = hw / 4, total = quads * a.N;
+  const bool has_mask = a.mask != nullptr && a.orig != nullptr;
+  const float blend = a.orig ? a.blend : 2.f;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const size_t n = i / quads, q = i - n * quads;
+    const float* s = a.src01 + n * 3 * hw + q * 4;
+    float v[3][4];
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+      const float4 t = *reinterpret_cast<const float4*>(s + (size_t)c * hw);
+      v[c][0] = t.x; v[c][1] = t.y; v[c][2] = t.z; v[c][3] = t.w;
+    }
+    uint32_t ow[3] = {0u, 0u, 0u};
+    if (a.orig) {
+      const uint32_t* o32 = reinterpret_cast<const uint32_t*>(a.orig + (n * hw + q * 4) * 3);
+      ow[0] = o32[0]; ow[1] = o32[1]; ow[2] = o32[2];
+    }
+    float al[4] = {0.f, 0.f, 0.f, 0.f};
+    if (a.mask) { const float4 t = *reinterpret_cast<const float4*>(a.mask + n * hw + q * 4); al[0] = t.x; al[1] = t.y; al[2] = t.z; al[3] = t.w; }
+    uint32_t outw[3] = {0u, 0u, 0u};
+#pragma unroll
+    for (int j = 0; j < 12; ++j) {                       // byte j of the 12-byte group = pixel j / 3, channel j % 3
+      const float og = a.orig ? u8_to_unit((float)((ow[j >> 2] >> ((j & 3) * 8)) & 0xFFu)) : 0.f;
+      const uint8_t b = post_pack(v[j % 3][j / 3], og, has_mask, al[j / 3], a.composite_mode, blend, a.blend_comp);
+      outw[j >> 2] |= (uint32_t)b << ((j & 3) * 8);
+    }
+    uint32_t* d32 = reinterpret_cast<uint32_t*>(a.out + (n * hw + q * 4) * 3);
+    d32[0] = outw[0]; d32[1] = outw[1]; d32[2] = outw[2];
+  }
+}
+
 cudaError_t launch_resize_post_pack(const ResizePackArgs& a, cudaStream_t stream) {
   const size_t total = (size_t)a.N * a.H * a.W;
+  const auto al16 = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; };
+  if (a.Hi == a.H && a.Wi == a.W && ((size_t)a.H * a.W) % 4 == 0 && al16(a.src01) && al16(a.out) && (!a.orig || al16(a.orig)) && (!a.mask || al16(a.mask))) {
+    const size_t quads = total / 4;
+    post_pack_x4_kernel<<<(int)std::min<size_t>((quads + 255) / 256, (size_t)148 * 16), 256, 0, stream>>>(a);
+    return cudaGetLastError();
+  }
   int blocks = (int)std::min<size_t>((total + 255) / 256, (size_t)148 * 16);
   resize_post_pack_kernel<<<blocks, 256, 0, stream>>>(a);
   return cudaGetLastError();
