@@ -177,6 +177,12 @@ def test_frame_pipeline_preserves_order_and_matches_per_frame_calls():
     out = torch.empty_like(frames)                                     # pageable out: staged
     assert torch.equal(pipe(frames.pin_memory(), out=out), want)
     assert torch.equal(pipe(frames.numpy()), want)                     # numpy in, second call reuses the staging
+    # >= 4 chunks: the optional ramped schedule (a quarter-size first and last chunk) -- here 1, 4, 4, 4, 4, 3, 1 -- with 2 and 3 slots, staged and direct
+    for slots in (2, 3):
+        p4 = m.FramePipeline(model, "raw_255", chunk=4, slots=slots, ramp=True)
+        assert torch.equal(p4(frames), want)
+        assert torch.equal(p4(frames.pin_memory(), out=torch.empty_like(frames)), want)
+    assert torch.equal(m.FramePipeline(model, "raw_255", chunk=4)(frames), want)
     # odd size + mask + blend go through the resize-back path, in order
     odd = synth.synthetic_frames_u8(5, 50, 70, seed=6)
     mask = torch.rand(5, 50, 70, generator=torch.Generator().manual_seed(2))
