@@ -26,6 +26,11 @@ struct LabEmaArgs {
   int N, H, W, init, smooth_L, smooth_ab;
   float aL, aL_comp, aC, aC_comp;               // fp32(alpha), fp32(1 - alpha): numpy narrows the Python doubles against fp32 arrays
 };
+// The two table look-ups of a frame are random 4-byte gathers (the tables are 64 MB each): walking the frames one by one chains
+// 2 * N dependent memory latencies per thread.  Only the EMA arithmetic is sequential over the frames, so the kernel works on blocks of
+// LAB_UNROLL frames: all RGB->LAB gathers of the block in flight together, then the (register-only) EMA recurrence, then all LAB->RGB
+// gathers together, then the stores.
+constexpr int LAB_UNROLL = 8;
 __global__ void __launch_bounds__(256) lab_ema_kernel(const __grid_constant__ LabEmaArgs a) {
   const int hw = a.H * a.W;
   for (int pix = blockIdx.x * blockDim.x + threadIdx.x; pix < hw; pix += gridDim.x * blockDim.x) {
@@ -34,13 +39,31 @@ __global__ void __launch_bounds__(256) lab_ema_kernel(const __grid_constant__ La
       if (a.smooth_L) st.L = a.prev_L[pix];
       if (a.smooth_ab) { st.a = a.prev_a[pix]; st.b = a.prev_b[pix]; }
     }
-    for (int n = 0; n < a.N; ++n) {
-      const uint8_t* px = a.frames + ((size_t)n * hw + pix) * 3;
-      const uint32_t lab = __ldg(a.rgb2lab + (((uint32_t)px[0] << 16) | ((uint32_t)px[1] << 8) | px[2]));
-      const uint32_t idx = lab_ema_step(lab, st, a.init && n == 0, a.smooth_L, a.smooth_ab, a.aL, a.aL_comp, a.aC, a.aC_comp);
-      const uint32_t rgb = __ldg(a.lab2rgb + idx);
-      uint8_t* o = a.out + ((size_t)n * hw + pix) * 3;
-      o[0] = (uint8_t)(rgb & 255u); o[1] = (uint8_t)((rgb >> 8) & 255u); o[2] = (uint8_t)((rgb >> 16) & 255u);
+    for (int n0 = 0; n0 < a.N; n0 += LAB_UNROLL) {
+      uint32_t v[LAB_UNROLL];
+#pragma unroll
+      for (int u = 0; u < LAB_UNROLL; ++u) {
+        if (n0 + u < a.N) {
+          const uint8_t* px = a.frames + ((size_t)(n0 + u) * hw + pix) * 3;
+          v[u] = ((uint32_t)px[0] << 16) | ((uint32_t)px[1] << 8) | px[2];
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < LAB_UNROLL; ++u)
+        if (n0 + u < a.N) v[u] = __ldg(a.rgb2lab + v[u]);
+#pragma unroll
+      for (int u = 0; u < LAB_UNROLL; ++u)
+        if (n0 + u < a.N) v[u] = lab_ema_step(v[u], st, a.init && n0 + u == 0, a.smooth_L, a.smooth_ab, a.aL, a.aL_comp, a.aC, a.aC_comp);
+#pragma unroll
+      for (int u = 0; u < LAB_UNROLL; ++u)
+        if (n0 + u < a.N) v[u] = __ldg(a.lab2rgb + v[u]);
+#pragma unroll
+      for (int u = 0; u < LAB_UNROLL; ++u) {
+        if (n0 + u < a.N) {
+          uint8_t* o = a.out + ((size_t)(n0 + u) * hw + pix) * 3;
+          o[0] = (uint8_t)(v[u] & 255u); o[1] = (uint8_t)((v[u] >> 8) & 255u); o[2] = (uint8_t)((v[u] >> 16) & 255u);
+        }
+      }
     }
     if (a.smooth_L) a.prev_L[pix] = st.L;
     if (a.smooth_ab) { a.prev_a[pix] = st.a; a.prev_b[pix] = st.b; }
