@@ -72,6 +72,29 @@ def prepare_region_crops(masks: torch.Tensor, configs: Sequence[RegionConfig], H
     return crops
 
 
+def models_needed(crops: Sequence[RegionCrop]) -> List[int]:
+    """Sorted model indices any region uses, the original (-1) excluded (region_blend.get_models_needed_for_regions, :2112-2127)."""
+    return sorted({mi for c in crops for mi in c.config.model_indices if mi >= 0})
+
+
+def regions_for_model(crops: Sequence[RegionCrop], model_idx: int) -> List[RegionCrop]:
+    """region_blend.get_regions_for_model (:2130-2141)."""
+    return [c for c in crops if model_idx in c.config.model_indices]
+
+
+def merge_bboxes(bboxes: Sequence[Tuple[int, int, int, int]]) -> Tuple[int, int, int, int]:
+    """The box containing all boxes; (0, 0, 0, 0) for none (region_blend.merge_bboxes, :2144-2162)."""
+    if not bboxes:
+        return (0, 0, 0, 0)
+    xs1, ys1, xs2, ys2 = zip(*bboxes)
+    return (min(xs1), min(ys1), max(xs2), max(ys2))
+
+
+def crop_coverage(crops: Sequence[RegionCrop], H: int, W: int) -> float:
+    """Styled pixels / frame pixels (> 1 with overlap): what `--region_optimize` saves (region_blend.compute_crop_coverage, :2165-2183)."""
+    return sum((c.padded_bbox[2] - c.padded_bbox[0]) * (c.padded_bbox[3] - c.padded_bbox[1]) for c in crops) / (H * W)
+
+
 def _pre(crop01: torch.Tensor, preset: str) -> torch.Tensor:
     """the three branches of pipeline.py:1357-1372"""
     if preset in ("imagenet_255", "imagenet_01"):
@@ -123,12 +146,9 @@ class RegionCropStyler:
             raise ValueError(f"frame_u8 must be a CUDA uint8 [{self.H}, {self.W}, 3] tensor")
         x01 = (frame_u8.permute(2, 0, 1).to(torch.float32) / torch.full((), 255.0, device=frame_u8.device)).contiguous()   # ToTensor, exact
         styled: Dict[int, Dict[int, torch.Tensor]] = {}
-        needed = sorted({mi for c in self.crops for mi in c.config.model_indices if mi >= 0})       # get_models_needed_for_regions
-        for mi in needed:
+        for mi in models_needed(self.crops):
             styled[mi] = {}
-            for c in self.crops:
-                if mi not in c.config.model_indices:
-                    continue
+            for c in regions_for_model(self.crops, mi):
                 x1, y1, x2, y2 = c.padded_bbox
                 ch, cw = y2 - y1, x2 - x1
                 crop = x01[:, y1:y2, x1:x2].unsqueeze(0)

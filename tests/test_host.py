@@ -179,3 +179,16 @@ def test_model_assignments_match_the_reference_function():
     assert len(table) >= 100
     for (nr, nm, mode, w, seed, oc), want in table:
         assert assign_models_to_regions(nr, nm, mode, w, seed, oc) == want, (nr, nm, mode, seed, oc)
+
+
+def test_crop_bookkeeping_helpers():
+    """region_blend.py:2112-2183 (models needed, regions of a model, merged box, coverage) on hand-checked values -- host list arithmetic."""
+    from neuralstyletransferv1_b200 import region_crops as rc
+    mk = lambda i, box, idx: rc.RegionCrop(i, box, box, torch.zeros(1, 1), rc.RegionConfig(idx, [1.0 / len(idx)] * len(idx)))
+    crops = [mk(0, (0, 0, 40, 30), [2]), mk(1, (30, 10, 100, 50), [0, -1]), mk(2, (5, 5, 25, 45), [2, 0])]
+    assert rc.models_needed(crops) == [0, 2]
+    assert [c.region_idx for c in rc.regions_for_model(crops, 0)] == [1, 2] and rc.regions_for_model(crops, 1) == []
+    assert [c.region_idx for c in rc.regions_for_model(crops, -1)] == [1]
+    assert rc.merge_bboxes([c.padded_bbox for c in crops]) == (0, 0, 100, 50) and rc.merge_bboxes([]) == (0, 0, 0, 0)
+    assert rc.crop_coverage(crops, 50, 100) == (40 * 30 + 70 * 40 + 20 * 40) / 5000
+    assert rc.pad_bbox((5, 5, 25, 45), 12, 100, 50) == (0, 0, 37, 50)
